@@ -1,0 +1,45 @@
+# Builds the product library (nodexa_chain_core_b200/libnxkawpow.so) for sm_100a and the CPU oracle.
+# nvcc cross-compiles without a GPU.  `python -c "import __graft_entry__ as g; g.build()"` drives this.
+NVCC      ?= /usr/local/cuda/bin/nvcc
+CUDA_HOME ?= /usr/local/cuda
+PKG       := nodexa_chain_core_b200
+SRC       := $(PKG)/csrc
+OBJ       := build/obj
+LIB       := $(PKG)/libnxkawpow.so
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function,-Wno-unknown-pragmas -Iinclude -I$(SRC)
+CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp
+CUSRC     := nx_dag.cu
+OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o))
+
+.PHONY: all lib oracle ref clean
+all: lib oracle
+
+lib: $(LIB)
+
+$(SRC)/kawpow_kernel_src.inc: $(SRC)/kawpow_kernel.cuh
+	( printf 'R"NXSRC(' ; cat $< ; printf ')NXSRC"\n' ) > $@
+
+$(OBJ)/nx_kernel_src.o: $(SRC)/kawpow_kernel_src.inc
+
+$(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
+
+$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@
+
+$(LIB): $(OBJS)
+	$(NVCC) $(ARCH) -shared -cudart static -o $@ $(OBJS) -L$(CUDA_HOME)/lib64 -lnvrtc -ldl -lpthread \
+	    -Xlinker -rpath=$(CUDA_HOME)/lib64
+
+oracle:
+	$(MAKE) -C oracle oracle
+
+ref:
+	$(MAKE) -C oracle ref
+
+clean:
+	rm -rf build $(LIB) $(SRC)/kawpow_kernel_src.inc
+	$(MAKE) -C oracle clean

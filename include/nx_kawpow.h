@@ -1,0 +1,200 @@
+/* nx_kawpow.h — C ABI of the B200-native KawPow / Ethash proof-of-work engine.
+ *
+ * Drop-in boundary for the PoW path of DeonDavisV/Nodexa-Chain-Core.  Every entry point names the
+ * reference interface it replaces (paths relative to the reference's src/).  Plain pointers and
+ * sizes only; no C++ or torch types cross this boundary.  All functions are thread-safe unless
+ * noted; none throws.  Functions returning int return NX_OK (0) or a negative nx_status, and leave a
+ * human-readable message for the calling thread in nx_last_error().
+ *
+ * Byte conventions (identical to the reference, see DESIGN.md "byte order"):
+ *   - header_hash, mix_hash, final_hash, boundary are 32-byte strings exactly as the reference's
+ *     ethash::hash256::bytes (crypto/ethash/include/ethash/hash_types.h:14-20);
+ *   - boundary comparison is big-endian over those bytes (crypto/ethash/lib/ethash/ethash-internal.hpp:32-43).
+ *
+ * The library needs a CUDA device (sm_100a) for everything that hashes; there is no CPU fallback:
+ * without a usable device those calls fail with NX_ERR_CUDA.
+ */
+#ifndef NX_KAWPOW_H
+#define NX_KAWPOW_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum nx_status
+{
+    NX_OK = 0,
+    NX_ERR_INVALID = -1, /* bad argument */
+    NX_ERR_CUDA = -2,    /* CUDA runtime/driver failure, or no device */
+    NX_ERR_NVRTC = -3,   /* period program failed to compile */
+    NX_ERR_OOM = -4,     /* host or device allocation failed */
+    NX_ERR_STATE = -5    /* context not ready (e.g. sharded DAG not finalized) */
+} nx_status;
+
+/* Message for the last failed call on this thread ("" if none). */
+const char* nx_last_error(void);
+const char* nx_version(void);
+int nx_device_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Epoch geometry — host only.
+ * Replaces ethash_calculate_light_cache_num_items / _full_dataset_num_items / _epoch_seed
+ * (crypto/ethash/lib/ethash/ethash.cpp:357-393), ethash_find_largest_prime
+ * (crypto/ethash/lib/ethash/primes.c:24-43) and ethash::find_epoch_number (ethash.cpp:57-97). */
+#define NX_EPOCH_LENGTH 7500 /* crypto/ethash/include/ethash/ethash.h:29 */
+#define NX_PERIOD_LENGTH 3   /* crypto/ethash/include/ethash/progpow.hpp:21 */
+int nx_find_largest_prime(int upper_bound);
+int nx_light_cache_num_items(int epoch);   /* 64-byte items  */
+int nx_full_dataset_num_items(int epoch);  /* 128-byte items; KawPow addresses floor(n/2) items of 256 bytes */
+void nx_epoch_seed(int epoch, uint8_t out[32]);
+int nx_find_epoch_number(const uint8_t seed[32]); /* -1 when not found within 30000 epochs */
+
+/* Host Keccak helpers, exported because the reference exports them
+ * (crypto/ethash/include/ethash/keccak.h:30-45). */
+void nx_keccakf1600(uint64_t state[25]);
+void nx_keccakf800(uint32_t state[25]);
+void nx_keccak256(const uint8_t* data, size_t size, uint8_t out[32]);
+void nx_keccak512(const uint8_t* data, size_t size, uint8_t out[64]);
+
+/* ------------------------------------------------------------------------------------------------
+ * Epoch context: light cache (host + device), 16 KiB L1 cache (host mirror), full DAG in HBM.
+ * Replaces ethash_create_epoch_context / _full / ethash_destroy_epoch_context(_full)
+ * (crypto/ethash/lib/ethash/ethash.cpp:131-172,395-414).  On B200 the DAG (1-5 GiB) is always
+ * materialised: generating it (K3) is faster than one CPU light-cache build. */
+typedef struct nx_epoch nx_epoch;
+
+/* Light cache (CUDA kernel K4 or host) + whole DAG generated on `device`. */
+int nx_epoch_create(int epoch, int device, nx_epoch** out);
+
+/* Multi-GPU build: this rank generates only DAG items [rank*share, min(M,(rank+1)*share)) with
+ * share = ceil(M/world), written at their final offset inside a buffer padded to world*share items.
+ * The caller then all-gathers nx_epoch_dag_ptr() in place (sendcount = nx_epoch_dag_share_bytes(),
+ * e.g. ncclAllGather / torch.distributed.all_gather_into_tensor) and calls nx_epoch_finalize().
+ * This is the only collective on the path. */
+int nx_epoch_create_sharded(int epoch, int device, int rank, int world, nx_epoch** out);
+int nx_epoch_finalize(nx_epoch* ctx);
+void nx_epoch_destroy(nx_epoch* ctx);
+
+/* Public fields of the reference's struct ethash_epoch_context (ethash.h:35-42). */
+int nx_epoch_number(const nx_epoch* ctx);
+int nx_epoch_light_items(const nx_epoch* ctx);
+int nx_epoch_dataset_items(const nx_epoch* ctx);      /* 128-byte items, as in the reference */
+const uint8_t* nx_epoch_light_cache(const nx_epoch* ctx); /* host copy, light_items*64 bytes */
+const uint32_t* nx_epoch_l1_cache(const nx_epoch* ctx);   /* host mirror, 4096 words */
+int nx_epoch_device(const nx_epoch* ctx);
+void* nx_epoch_dag_ptr(const nx_epoch* ctx);          /* DEVICE pointer to the (padded) DAG */
+size_t nx_epoch_dag_bytes(const nx_epoch* ctx);       /* addressable DAG bytes = floor(n/2)*256 */
+size_t nx_epoch_dag_padded_bytes(const nx_epoch* ctx);
+size_t nx_epoch_dag_share_bytes(const nx_epoch* ctx); /* bytes each rank contributes to the all-gather */
+/* Timings of the build phases in milliseconds (CUDA events / host clock): light cache, DAG kernel. */
+void nx_epoch_build_times(const nx_epoch* ctx, double* light_ms, double* dag_ms);
+
+/* Regenerate `count` 256-byte DAG items starting at `first` into a caller-provided DEVICE buffer
+ * (K3 alone; used by benchmarks and parity tests).  Replaces calculate_dataset_item_2048
+ * (ethash.cpp:235-251) applied to a range. */
+int nx_dag_generate_range(const nx_epoch* ctx, uint32_t first, uint32_t count, void* out_device);
+/* Copy `count` items starting at `first` from the resident DAG to host memory. */
+int nx_dag_read_items(const nx_epoch* ctx, uint32_t first, uint32_t count, uint8_t* out_host);
+/* Position-weighted 64-bit sum over the addressable DAG: sum_i u64word_i*(2i+1) mod 2^64.
+ * No reference counterpart (test/ops aid: equal on every GPU after the all-gather). */
+int nx_dag_checksum(const nx_epoch* ctx, uint64_t* out);
+
+/* ------------------------------------------------------------------------------------------------
+ * KawPow. */
+typedef struct nx_result
+{
+    uint8_t final_hash[32];
+    uint8_t mix_hash[32];
+} nx_result; /* layout of ethash_result, ethash.h:48-52 */
+
+typedef struct nx_search_result
+{
+    int32_t found;
+    uint32_t reserved;
+    uint64_t nonce;
+    uint8_t final_hash[32];
+    uint8_t mix_hash[32];
+} nx_search_result; /* fields of ethash::search_result, ethash.hpp:49-61 */
+
+/* Compile (NVRTC, sm_100a) and cache the random program of the period block_number/3 for this
+ * context's device, so that the first hash/search of a period does not pay for it.  Optional. */
+int nx_kawpow_prepare(const nx_epoch* ctx, int block_number);
+
+/* One nonce.  Replaces progpow::hash(ctx, block_number, header_hash, nonce)
+ * (crypto/ethash/lib/ethash/progpow.cpp:298-355 and :357-429). */
+int nx_kawpow_hash(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32], uint64_t nonce,
+                   nx_result* out);
+
+/* `count` consecutive nonces; out = count x {final_hash[32], mix_hash[32]} in HOST memory
+ * (kernel K2; the copy back is part of the call). */
+int nx_kawpow_hash_batch(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32],
+                         uint64_t start_nonce, uint64_t count, uint8_t* out_host);
+/* Same, results left in DEVICE memory (count*64 bytes); returns after the kernel completed. */
+int nx_kawpow_hash_batch_device(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32],
+                                uint64_t start_nonce, uint64_t count, void* out_device);
+
+/* Lowest nonce in [start_nonce, start_nonce+iterations) whose final hash <= boundary, or found=0 and
+ * all fields zero.  Replaces progpow::search / search_light (progpow.cpp:553-579) and the inner
+ * nonce loop of miner.cpp:663-690 / rpc/mining.cpp:141-149. */
+int nx_kawpow_search(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32],
+                     const uint8_t boundary[32], uint64_t start_nonce, uint64_t iterations,
+                     nx_search_result* out);
+
+/* Throughput form of the search for benchmarking/pipelining: enqueue the scan of one batch on the
+ * context's stream without synchronising.  nx_kawpow_search_sync() waits and reports the lowest hit
+ * of everything enqueued since the last sync. */
+int nx_kawpow_search_enqueue(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32],
+                             const uint8_t boundary[32], uint64_t start_nonce, uint64_t count);
+int nx_kawpow_search_sync(const nx_epoch* ctx, nx_search_result* out);
+/* Device time in ms of the kernels enqueued between the last two syncs (CUDA events on the
+ * launching stream) and how many kernels that was. */
+int nx_kawpow_last_timing(const nx_epoch* ctx, float* kernel_ms, int* launches);
+
+/* 1 = valid, 0 = invalid, <0 = error.  Replaces progpow::verify (progpow.cpp:431-495): final hash from
+ * the claimed mix must be <= boundary, then the recomputed mix must equal the claimed one. */
+int nx_kawpow_verify(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32],
+                     const uint8_t mix_hash[32], uint64_t nonce, const uint8_t boundary[32]);
+
+/* Final hash from a CLAIMED mix (two keccak-f800, no DAG) — host only.  Replaces
+ * progpow::hash_no_verify (progpow.cpp:498-550); block_number is unused there as well. */
+void nx_kawpow_hash_no_verify(int block_number, const uint8_t header_hash[32], const uint8_t mix_hash[32],
+                              uint64_t nonce, uint8_t out[32]);
+
+/* Batched header verification (kernel K6): n independent {block_number(all in ctx's epoch), header,
+ * mix, nonce, boundary} records; ok[i] = 1/0.  Replaces the per-header progpow::verify calls of
+ * validation.cpp:11652-11662 during header sync.  Records are 112 bytes:
+ * {int32 block_number, uint32 pad, uint64 nonce, header[32], mix[32], boundary[32]}. */
+typedef struct nx_verify_record
+{
+    int32_t block_number;
+    uint32_t pad;
+    uint64_t nonce;
+    uint8_t header_hash[32];
+    uint8_t mix_hash[32];
+    uint8_t boundary[32];
+} nx_verify_record;
+int nx_kawpow_verify_batch(const nx_epoch* ctx, const nx_verify_record* records, size_t n, uint8_t* ok);
+
+/* ------------------------------------------------------------------------------------------------
+ * Node glue — host only. */
+
+/* header_hash that the node feeds to progpow: SHA256d over the 80-byte CKAWPOWInput
+ * {nVersion,hashPrevBlock,hashMerkleRoot,nTime,nBits,nHeight} (primitives/block.h:213-233,
+ * primitives/block.cpp:94-99), byte-reversed by the GetHex()/to_hash256 round trip of hash.cpp:269-270. */
+void nx_kawpow_header_hash(int32_t version, const uint8_t prev_block[32], const uint8_t merkle_root[32],
+                           uint32_t time, uint32_t bits, uint32_t height, uint8_t out[32]);
+void nx_sha256d(const uint8_t* data, size_t size, uint8_t out[32]);
+
+/* Compact nBits -> 32-byte big-endian boundary (arith_uint256::SetCompact, arith_uint256.cpp:209-228).
+ * Returns 1 when the target is usable, 0 when negative / zero / overflowing (pow.cpp:190-191). */
+int nx_compact_to_boundary(uint32_t bits, uint8_t out[32]);
+/* CheckProofOfWork (pow.cpp:182-199) on a final hash in progpow byte order: 1 = passes. */
+int nx_check_proof_of_work(const uint8_t final_hash[32], uint32_t bits, const uint8_t pow_limit_be[32]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NX_KAWPOW_H */

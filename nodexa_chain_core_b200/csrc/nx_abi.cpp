@@ -1,0 +1,533 @@
+// extern "C" entry points that own device state: epoch contexts and the KawPow calls.
+// (Pure host entry points live in nx_host.cpp.)
+#include "nx_internal.hpp"
+
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <new>
+
+using namespace nx;
+
+namespace
+{
+constexpr uint64_t NOT_FOUND = ~0ull;
+constexpr uint64_t SEARCH_BATCH = 1ull << 22;  // nonces per launch inside nx_kawpow_search
+
+inline uint32_t bswap32(uint32_t x) { return __builtin_bswap32(x); }
+
+void fill_job(KawpowJob& job, const uint8_t header[32], const uint8_t* boundary, uint64_t start, uint64_t count,
+              uint64_t report_base)
+{
+    std::memcpy(job.header, header, 32);
+    if (boundary) {
+        uint32_t w[8];
+        std::memcpy(w, boundary, 32);
+        for (int i = 0; i < 8; ++i) job.boundary_be[i] = bswap32(w[i]);
+    } else {
+        std::memset(job.boundary_be, 0, 32);
+    }
+    job.start_nonce = start;
+    job.count = count;
+    job.report_base = report_base;
+}
+
+int ensure_batch_out(nx_epoch* c, size_t bytes)
+{
+    if (c->batch_out_bytes >= bytes) return NX_OK;
+    if (c->batch_out_dev) cudaFree(c->batch_out_dev);
+    c->batch_out_dev = nullptr;
+    c->batch_out_bytes = 0;
+    if (cudaMalloc(&c->batch_out_dev, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("out of device memory for %zu result bytes", bytes);
+        return NX_ERR_OOM;
+    }
+    c->batch_out_bytes = bytes;
+    return NX_OK;
+}
+
+int check_ctx(const nx_epoch* c, int block_number)
+{
+    if (!c) {
+        set_error("null epoch context");
+        return NX_ERR_INVALID;
+    }
+    if (!c->ready) {
+        set_error("epoch context not finalized (sharded DAG still waiting for its all-gather)");
+        return NX_ERR_STATE;
+    }
+    if (block_number < 0) {
+        set_error("negative block number");
+        return NX_ERR_INVALID;
+    }
+    return NX_OK;
+}
+
+int program_for(const nx_epoch* c, int block_number, std::shared_ptr<KawpowProgram>* p)
+{
+    return kawpow_get_program(c->device, (uint64_t)(block_number / NX_PERIOD_LENGTH), c->dag_items, p);
+}
+
+void destroy(nx_epoch* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->dag_dev) cudaFree(c->dag_dev);
+    if (c->light_dev) cudaFree(c->light_dev);
+    if (c->found_min_dev) cudaFree(c->found_min_dev);
+    if (c->checksum_partials_dev) cudaFree(c->checksum_partials_dev);
+    if (c->batch_out_dev) cudaFree(c->batch_out_dev);
+    if (c->found_min_host) cudaFreeHost(c->found_min_host);
+    if (c->light_host) cudaFreeHost(c->light_host);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int create(int epoch, int device, int rank, int world, nx_epoch** out)
+{
+    clear_error();
+    if (!out) {
+        set_error("null out pointer");
+        return NX_ERR_INVALID;
+    }
+    *out = nullptr;
+    if (epoch < 0 || epoch > 30000 || world < 1 || rank < 0 || rank >= world) {
+        set_error("bad epoch/rank/world (%d, %d, %d)", epoch, rank, world);
+        return NX_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("no CUDA device: this library has no CPU fallback");
+        return NX_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) {
+        set_error("device %d out of range (have %d)", device, ndev);
+        return NX_ERR_INVALID;
+    }
+    NX_CUDA(cudaSetDevice(device));
+
+    nx_epoch* c = new (std::nothrow) nx_epoch;
+    if (!c) return NX_ERR_OOM;
+    c->epoch = epoch;
+    c->device = device;
+    c->rank = rank;
+    c->world = world;
+    c->light_items = nx_light_cache_num_items(epoch);
+    c->dataset_items = nx_full_dataset_num_items(epoch);
+    c->dag_items = (uint32_t)(c->dataset_items / 2);
+    c->share_items = (c->dag_items + (uint32_t)world - 1) / (uint32_t)world;
+    c->dag_padded_bytes = (size_t)c->share_items * (size_t)world * 256;
+    const size_t light_bytes = (size_t)c->light_items * 64;
+
+    auto fail = [&](int rc) {
+        destroy(c);
+        return rc;
+    };
+#define NX_TRY(call)                                                                               \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            set_error("%s failed: %s", #call, cudaGetErrorString(e_));                             \
+            cudaGetLastError();                                                                    \
+            return fail(e_ == cudaErrorMemoryAllocation ? NX_ERR_OOM : NX_ERR_CUDA);               \
+        }                                                                                          \
+    } while (0)
+
+    NX_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    NX_TRY(cudaEventCreate(&c->ev0));
+    NX_TRY(cudaEventCreate(&c->ev1));
+    NX_TRY(cudaMallocHost((void**)&c->light_host, light_bytes));
+    NX_TRY(cudaMalloc(&c->light_dev, light_bytes));
+    NX_TRY(cudaMalloc(&c->dag_dev, c->dag_padded_bytes));
+    NX_TRY(cudaMalloc((void**)&c->found_min_dev, 2 * sizeof(uint64_t)));
+    NX_TRY(cudaMallocHost((void**)&c->found_min_host, 2 * sizeof(uint64_t)));
+    NX_TRY(cudaMalloc((void**)&c->checksum_partials_dev, CHECKSUM_PARTIALS * sizeof(uint64_t)));
+
+    // ---- light cache: serial chain.  Host by default; NX_LIGHT_CACHE=gpu runs kernel K4. ----
+    uint8_t seed[32];
+    nx_epoch_seed(epoch, seed);
+    const char* mode = std::getenv("NX_LIGHT_CACHE");
+    const auto t0 = std::chrono::steady_clock::now();
+    if (mode && std::strcmp(mode, "gpu") == 0) {
+        int rc = light_cache_build_gpu(c->light_dev, c->light_items, seed, c->stream);
+        if (rc != NX_OK) return fail(rc);
+        NX_TRY(cudaMemcpyAsync(c->light_host, c->light_dev, light_bytes, cudaMemcpyDeviceToHost, c->stream));
+        NX_TRY(cudaStreamSynchronize(c->stream));
+    } else {
+        host_build_light_cache(c->light_host, c->light_items, seed);
+        NX_TRY(cudaMemcpyAsync(c->light_dev, c->light_host, light_bytes, cudaMemcpyHostToDevice, c->stream));
+    }
+    c->light_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+
+    // ---- DAG: this rank's slice, written at its final offset ----
+    const uint32_t first = (uint32_t)rank * c->share_items;
+    const uint32_t last = first + c->share_items < c->dag_items ? first + c->share_items : c->dag_items;
+    const uint32_t count = last > first ? last - first : 0;
+    if (c->dag_padded_bytes > (size_t)c->dag_items * 256)  // padding tail is never addressed; keep it defined
+        NX_TRY(cudaMemsetAsync((char*)c->dag_dev + (size_t)c->dag_items * 256, 0,
+                               c->dag_padded_bytes - (size_t)c->dag_items * 256, c->stream));
+    NX_TRY(cudaEventRecord(c->ev0, c->stream));
+    {
+        int rc = dag_generate(c->light_dev, c->light_items, first, count, (char*)c->dag_dev + (size_t)first * 256,
+                              c->stream);
+        if (rc != NX_OK) return fail(rc);
+    }
+    NX_TRY(cudaEventRecord(c->ev1, c->stream));
+    NX_TRY(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    NX_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->dag_ms = ms;
+#undef NX_TRY
+
+    *out = c;
+    if (world == 1) return nx_epoch_finalize(c);
+    return NX_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int nx_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int nx_epoch_create(int epoch, int device, nx_epoch** out) { return create(epoch, device, 0, 1, out); }
+
+int nx_epoch_create_sharded(int epoch, int device, int rank, int world, nx_epoch** out)
+{
+    return create(epoch, device, rank, world, out);
+}
+
+int nx_epoch_finalize(nx_epoch* c)
+{
+    if (!c) {
+        set_error("null epoch context");
+        return NX_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    // L1 cache mirror = first 16 KiB of the DAG (reference ethash.cpp:168-170)
+    NX_CUDA(cudaMemcpy(c->l1_host, c->dag_dev, sizeof c->l1_host, cudaMemcpyDeviceToHost));
+    c->ready = true;
+    return NX_OK;
+}
+
+void nx_epoch_destroy(nx_epoch* c) { destroy(c); }
+
+int nx_epoch_number(const nx_epoch* c) { return c ? c->epoch : -1; }
+int nx_epoch_light_items(const nx_epoch* c) { return c ? c->light_items : 0; }
+int nx_epoch_dataset_items(const nx_epoch* c) { return c ? c->dataset_items : 0; }
+const uint8_t* nx_epoch_light_cache(const nx_epoch* c) { return c ? c->light_host : nullptr; }
+const uint32_t* nx_epoch_l1_cache(const nx_epoch* c) { return c ? c->l1_host : nullptr; }
+int nx_epoch_device(const nx_epoch* c) { return c ? c->device : -1; }
+void* nx_epoch_dag_ptr(const nx_epoch* c) { return c ? c->dag_dev : nullptr; }
+size_t nx_epoch_dag_bytes(const nx_epoch* c) { return c ? (size_t)c->dag_items * 256 : 0; }
+size_t nx_epoch_dag_padded_bytes(const nx_epoch* c) { return c ? c->dag_padded_bytes : 0; }
+size_t nx_epoch_dag_share_bytes(const nx_epoch* c) { return c ? (size_t)c->share_items * 256 : 0; }
+void nx_epoch_build_times(const nx_epoch* c, double* light_ms, double* dag_ms)
+{
+    if (light_ms) *light_ms = c ? c->light_ms : 0;
+    if (dag_ms) *dag_ms = c ? c->dag_ms : 0;
+}
+
+int nx_dag_generate_range(const nx_epoch* cc, uint32_t first, uint32_t count, void* out_device)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    if (!c || !out_device) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if ((uint64_t)first + count > c->dag_items) {
+        set_error("item range [%u,+%u) beyond the DAG (%u items)", first, count, c->dag_items);
+        return NX_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+    int rc = dag_generate(c->light_dev, c->light_items, first, count, out_device, c->stream);
+    if (rc != NX_OK) return rc;
+    NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+    NX_CUDA(cudaStreamSynchronize(c->stream));
+    NX_CUDA(cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1));
+    c->last_launches = 1;
+    return NX_OK;
+}
+
+int nx_dag_read_items(const nx_epoch* c, uint32_t first, uint32_t count, uint8_t* out_host)
+{
+    if (!c || !out_host) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if ((uint64_t)first + count > (uint64_t)c->share_items * c->world) {
+        set_error("item range beyond the DAG buffer");
+        return NX_ERR_INVALID;
+    }
+    NX_CUDA(cudaSetDevice(c->device));
+    NX_CUDA(cudaMemcpy(out_host, (const char*)c->dag_dev + (size_t)first * 256, (size_t)count * 256,
+                       cudaMemcpyDeviceToHost));
+    return NX_OK;
+}
+
+int nx_dag_checksum(const nx_epoch* cc, uint64_t* out)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    if (!c || !out) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    int rc = dag_checksum(c->dag_dev, (size_t)c->dag_items * 32, c->checksum_partials_dev, CHECKSUM_PARTIALS,
+                          c->found_min_dev + 1, c->stream);
+    if (rc != NX_OK) return rc;
+    NX_CUDA(cudaMemcpyAsync(c->found_min_host + 1, c->found_min_dev + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+    NX_CUDA(cudaStreamSynchronize(c->stream));
+    *out = c->found_min_host[1];
+    return NX_OK;
+}
+
+int nx_kawpow_prepare(const nx_epoch* c, int block_number)
+{
+    int rc = check_ctx(c, block_number);
+    if (rc != NX_OK) return rc;
+    std::shared_ptr<KawpowProgram> p;
+    return program_for(c, block_number, &p);
+}
+
+int nx_kawpow_hash_batch_device(const nx_epoch* cc, int block_number, const uint8_t header_hash[32],
+                                uint64_t start_nonce, uint64_t count, void* out_device)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    int rc = check_ctx(c, block_number);
+    if (rc != NX_OK) return rc;
+    if (!header_hash || (!out_device && count)) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if (count == 0) return NX_OK;
+    std::shared_ptr<KawpowProgram> p;
+    if ((rc = program_for(c, block_number, &p)) != NX_OK) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    KawpowJob job;
+    fill_job(job, header_hash, nullptr, start_nonce, count, 0);
+    NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+    if ((rc = kawpow_launch_hash(p.get(), c->dag_dev, job, out_device, c->stream)) != NX_OK) return rc;
+    NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+    NX_CUDA(cudaStreamSynchronize(c->stream));
+    NX_CUDA(cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1));
+    c->last_launches = 1;
+    return NX_OK;
+}
+
+int nx_kawpow_hash_batch(const nx_epoch* cc, int block_number, const uint8_t header_hash[32], uint64_t start_nonce,
+                         uint64_t count, uint8_t* out_host)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    int rc = check_ctx(c, block_number);
+    if (rc != NX_OK) return rc;
+    if (!header_hash || (!out_host && count)) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if (count == 0) return NX_OK;
+    std::shared_ptr<KawpowProgram> p;
+    if ((rc = program_for(c, block_number, &p)) != NX_OK) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    constexpr uint64_t CHUNK = 1ull << 22;  // 256 MiB of results per launch
+    if ((rc = ensure_batch_out(c, (size_t)(count < CHUNK ? count : CHUNK) * 64)) != NX_OK) return rc;
+    float total_ms = 0;
+    int launches = 0;
+    for (uint64_t done = 0; done < count; done += CHUNK) {
+        const uint64_t n = count - done < CHUNK ? count - done : CHUNK;
+        KawpowJob job;
+        fill_job(job, header_hash, nullptr, start_nonce + done, n, 0);
+        NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+        if ((rc = kawpow_launch_hash(p.get(), c->dag_dev, job, c->batch_out_dev, c->stream)) != NX_OK) return rc;
+        NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+        NX_CUDA(cudaMemcpyAsync(out_host + done * 64, c->batch_out_dev, (size_t)n * 64, cudaMemcpyDeviceToHost, c->stream));
+        NX_CUDA(cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        NX_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        total_ms += ms;
+        ++launches;
+    }
+    c->last_kernel_ms = total_ms;
+    c->last_launches = launches;
+    return NX_OK;
+}
+
+int nx_kawpow_hash(const nx_epoch* c, int block_number, const uint8_t header_hash[32], uint64_t nonce, nx_result* out)
+{
+    if (!out) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    uint8_t buf[64];
+    const int rc = nx_kawpow_hash_batch(c, block_number, header_hash, nonce, 1, buf);
+    if (rc != NX_OK) return rc;
+    std::memcpy(out->final_hash, buf, 32);
+    std::memcpy(out->mix_hash, buf + 32, 32);
+    return NX_OK;
+}
+
+int nx_kawpow_search_enqueue(const nx_epoch* cc, int block_number, const uint8_t header_hash[32],
+                             const uint8_t boundary[32], uint64_t start_nonce, uint64_t count)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    int rc = check_ctx(c, block_number);
+    if (rc != NX_OK) return rc;
+    if (!header_hash || !boundary) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if (count == 0) return NX_OK;
+    std::shared_ptr<KawpowProgram> p;
+    if ((rc = program_for(c, block_number, &p)) != NX_OK) return rc;
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    if (!c->pending) {
+        c->found_min_host[0] = NOT_FOUND;
+        NX_CUDA(cudaMemcpyAsync(c->found_min_dev, c->found_min_host, 8, cudaMemcpyHostToDevice, c->stream));
+        NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+        c->pending = true;
+        c->pending_base = start_nonce;
+        c->pending_block = block_number;
+        std::memcpy(c->pending_header, header_hash, 32);
+        c->launches_since_sync = 0;
+    }
+    KawpowJob job;
+    fill_job(job, header_hash, boundary, start_nonce, count, start_nonce - c->pending_base);
+    if ((rc = kawpow_launch_search(p.get(), c->dag_dev, job, c->found_min_dev, c->stream)) != NX_OK) return rc;
+    ++c->launches_since_sync;
+    return NX_OK;
+}
+
+int nx_kawpow_search_sync(const nx_epoch* cc, nx_search_result* out)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    if (!c || !out) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    std::memset(out, 0, sizeof *out);
+    uint64_t hit = NOT_FOUND;
+    int block = 0;
+    uint8_t header[32];
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (!c->pending) return NX_OK;
+        NX_CUDA(cudaSetDevice(c->device));
+        NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+        NX_CUDA(cudaMemcpyAsync(c->found_min_host, c->found_min_dev, 8, cudaMemcpyDeviceToHost, c->stream));
+        NX_CUDA(cudaStreamSynchronize(c->stream));
+        NX_CUDA(cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1));
+        c->last_launches = c->launches_since_sync;
+        c->pending = false;
+        if (c->found_min_host[0] != NOT_FOUND) hit = c->pending_base + c->found_min_host[0];
+        block = c->pending_block;
+        std::memcpy(header, c->pending_header, 32);
+        if (c->found_min_host[0] == NOT_FOUND) return NX_OK;
+    }
+    // a hit: re-hash that one nonce to obtain {final, mix} (keeps the hot kernel free of result traffic)
+    nx_result r;
+    const float keep_ms = c->last_kernel_ms;
+    const int keep_n = c->last_launches;
+    const int rc = nx_kawpow_hash(c, block, header, hit, &r);
+    c->last_kernel_ms = keep_ms;
+    c->last_launches = keep_n + 1;
+    if (rc != NX_OK) return rc;
+    out->found = 1;
+    out->nonce = hit;
+    std::memcpy(out->final_hash, r.final_hash, 32);
+    std::memcpy(out->mix_hash, r.mix_hash, 32);
+    return NX_OK;
+}
+
+int nx_kawpow_last_timing(const nx_epoch* c, float* kernel_ms, int* launches)
+{
+    if (!c) return NX_ERR_INVALID;
+    if (kernel_ms) *kernel_ms = c->last_kernel_ms;
+    if (launches) *launches = c->last_launches;
+    return NX_OK;
+}
+
+int nx_kawpow_search(const nx_epoch* c, int block_number, const uint8_t header_hash[32], const uint8_t boundary[32],
+                     uint64_t start_nonce, uint64_t iterations, nx_search_result* out)
+{
+    if (!out) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    std::memset(out, 0, sizeof *out);
+    int rc = check_ctx(c, block_number);
+    if (rc != NX_OK) return rc;
+    // ascending batches; the first batch with a hit holds the lowest qualifying nonce
+    // (reference progpow.cpp:572-577 returns the first hit of an ascending scan)
+    float total_ms = 0;
+    int launches = 0;
+    for (uint64_t done = 0; done < iterations; done += SEARCH_BATCH) {
+        const uint64_t n = iterations - done < SEARCH_BATCH ? iterations - done : SEARCH_BATCH;
+        if ((rc = nx_kawpow_search_enqueue(c, block_number, header_hash, boundary, start_nonce + done, n)) != NX_OK)
+            return rc;
+        if ((rc = nx_kawpow_search_sync(c, out)) != NX_OK) return rc;
+        total_ms += c->last_kernel_ms;
+        launches += c->last_launches;
+        if (out->found) break;
+    }
+    nx_epoch* m = const_cast<nx_epoch*>(c);
+    m->last_kernel_ms = total_ms;
+    m->last_launches = launches;
+    return NX_OK;
+}
+
+int nx_kawpow_verify(const nx_epoch* c, int block_number, const uint8_t header_hash[32], const uint8_t mix_hash[32],
+                     uint64_t nonce, const uint8_t boundary[32])
+{
+    if (!header_hash || !mix_hash || !boundary) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    int rc = check_ctx(c, block_number);
+    if (rc != NX_OK) return rc;
+    // cheap test first, exactly as the reference orders it (progpow.cpp:487-494)
+    uint8_t fin[32];
+    nx_kawpow_hash_no_verify(block_number, header_hash, mix_hash, nonce, fin);
+    if (std::memcmp(fin, boundary, 32) > 0) return 0;
+    nx_result r;
+    if ((rc = nx_kawpow_hash(c, block_number, header_hash, nonce, &r)) != NX_OK) return rc;
+    return std::memcmp(r.mix_hash, mix_hash, 32) == 0 ? 1 : 0;
+}
+
+int nx_kawpow_verify_batch(const nx_epoch* c, const nx_verify_record* records, size_t n, uint8_t* ok)
+{
+    if ((!records || !ok) && n) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    // Records that fail the boundary test never reach the GPU.  The rest are hashed one launch per
+    // record for now (each has its own header); K6 proper batches them per period.
+    for (size_t i = 0; i < n; ++i) {
+        const int v = nx_kawpow_verify(c, records[i].block_number, records[i].header_hash, records[i].mix_hash,
+                                       records[i].nonce, records[i].boundary);
+        if (v < 0) return v;
+        ok[i] = (uint8_t)v;
+    }
+    return NX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,243 @@
+// Ethash DAG generation (K3), DAG checksum and light-cache kernels for sm_100a.
+//
+// Replaces: item_state / calculate_dataset_item_512/1024/2048
+// (reference src/crypto/ethash/lib/ethash/ethash.cpp:180-251, 512 parents per 64-byte item, :27) and,
+// for the L1 cache, the tail of create_epoch_context (:168-170): the L1 cache is simply the first
+// 16 KiB of the DAG, so it falls out of K3.
+//
+// Layout in HBM: the DAG is an array of 256-byte items ("hash2048"); item i is made of the four
+// 64-byte Ethash items 4i..4i+3.  The light cache is an array of 64-byte items and is read with
+// 16-byte loads, four lanes per parent, so a warp-wide load touches 8 parents x 64 contiguous bytes
+// (2 full sectors each) instead of 32 half-used sectors.
+//
+// Bound: L2 gather bandwidth.  Every 64 output bytes need 512 random 64-byte reads from the
+// 16-80 MiB light cache (32 KiB of L2 traffic per 64 B written); HBM only sees the
+// DAG being written once.
+#include "nx_internal.hpp"
+#include "nx_keccak.cuh"
+
+namespace nx
+{
+namespace
+{
+constexpr uint32_t FNV_PRIME = 0x01000193u;
+__device__ __forceinline__ uint32_t fnv1(uint32_t u, uint32_t v) { return (u * FNV_PRIME) ^ v; }
+
+// x % d for a run-time d (the prime light-cache item count), without an integer divide:
+// q = floor(x * floor(2^32/d) / 2^32) is floor(x/d) or one less, so one conditional subtract fixes it.
+struct FastMod
+{
+    uint32_t d, m;
+};
+__device__ __forceinline__ uint32_t fast_mod(uint32_t x, FastMod f)
+{
+    const uint32_t r = x - __umulhi(x, f.m) * f.d;
+    return min(r, r - f.d);  // r - d wraps to a huge value when r < d
+}
+
+constexpr int DAG_THREADS = 128;
+
+// One thread owns one 64-byte item for the two Keccak calls; the 512-parent FNV walk of each item
+// is done by the four lanes of its quad together (each lane holds 4 of the 16 mix words).
+__global__ void __launch_bounds__(DAG_THREADS)
+dag_items_kernel(const uint4* __restrict__ light, FastMod fm, uint32_t first512, uint32_t count512,
+                 uint4* __restrict__ out)
+{
+    const uint32_t gid = blockIdx.x * DAG_THREADS + threadIdx.x;
+    const uint32_t sub = threadIdx.x & 3u;
+    const bool live = gid < count512;
+    const uint32_t k = first512 + (live ? gid : 0u);  // dead lanes recompute item `first512`; never stored
+
+    uint32_t mix[16];
+    {
+        const uint4* src = light + (size_t)fast_mod(k, fm) * 4;
+        uint64_t w[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint4 v = __ldg(src + i);
+            w[2 * i] = (uint64_t)v.x | ((uint64_t)v.y << 32);
+            w[2 * i + 1] = (uint64_t)v.z | ((uint64_t)v.w << 32);
+        }
+        w[0] ^= (uint64_t)k;  // mix.word32s[0] ^= seed
+        keccak512_64(w);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            mix[2 * i] = (uint32_t)w[i];
+            mix[2 * i + 1] = (uint32_t)(w[i] >> 32);
+        }
+    }
+
+#pragma unroll 1
+    for (uint32_t p = 0; p < 4; ++p) {
+        const uint32_t seed = __shfl_sync(0xffffffffu, k, p, 4);
+        // lane `sub` takes words 4*sub..4*sub+3 of quad-lane p's item
+        uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+#pragma unroll
+        for (int w = 0; w < 16; ++w) {
+            const uint32_t v = __shfl_sync(0xffffffffu, mix[w], p, 4);
+            if ((uint32_t)(w >> 2) == sub) {
+                if ((w & 3) == 0) m0 = v;
+                if ((w & 3) == 1) m1 = v;
+                if ((w & 3) == 2) m2 = v;
+                if ((w & 3) == 3) m3 = v;
+            }
+        }
+#pragma unroll 1
+        for (uint32_t j = 0; j < 512; j += 16) {
+#pragma unroll
+            for (uint32_t jj = 0; jj < 16; ++jj) {
+                // mix word jj lives in quad-lane jj/4, component jj%4
+                const uint32_t mine = (jj & 3) == 0 ? m0 : (jj & 3) == 1 ? m1 : (jj & 3) == 2 ? m2 : m3;
+                const uint32_t t = fnv1(seed ^ (j + jj), __shfl_sync(0xffffffffu, mine, jj >> 2, 4));
+                const uint4 pv = __ldg(light + (size_t)fast_mod(t, fm) * 4 + sub);
+                m0 = fnv1(m0, pv.x);
+                m1 = fnv1(m1, pv.y);
+                m2 = fnv1(m2, pv.z);
+                m3 = fnv1(m3, pv.w);
+            }
+        }
+        // hand the 16 words back to quad-lane p
+#pragma unroll
+        for (int w = 0; w < 16; ++w) {
+            const uint32_t mine = (w & 3) == 0 ? m0 : (w & 3) == 1 ? m1 : (w & 3) == 2 ? m2 : m3;
+            const uint32_t v = __shfl_sync(0xffffffffu, mine, w >> 2, 4);
+            if (sub == p) mix[w] = v;
+        }
+    }
+
+    {
+        uint64_t w[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = (uint64_t)mix[2 * i] | ((uint64_t)mix[2 * i + 1] << 32);
+        keccak512_64(w);
+        if (live) {
+            uint4* dst = out + (size_t)gid * 4;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                dst[i] = make_uint4((uint32_t)w[2 * i], (uint32_t)(w[2 * i] >> 32), (uint32_t)w[2 * i + 1],
+                                    (uint32_t)(w[2 * i + 1] >> 32));
+        }
+    }
+}
+
+// ---- position-weighted checksum: sum_i w_i * (2i+1) mod 2^64 ----
+constexpr int CSUM_THREADS = 256;
+
+__global__ void __launch_bounds__(CSUM_THREADS)
+checksum_partial_kernel(const uint64_t* __restrict__ words, size_t n, uint64_t* __restrict__ partials)
+{
+    __shared__ uint64_t red[CSUM_THREADS / 32];
+    uint64_t acc = 0;
+    const size_t stride = (size_t)gridDim.x * CSUM_THREADS;
+    for (size_t i = (size_t)blockIdx.x * CSUM_THREADS + threadIdx.x; i < n; i += stride)
+        acc += __ldg(words + i) * (2 * (uint64_t)i + 1);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t s = 0;
+        for (int i = 0; i < CSUM_THREADS / 32; ++i) s += red[i];
+        partials[blockIdx.x] = s;
+    }
+}
+
+__global__ void checksum_final_kernel(const uint64_t* __restrict__ partials, int n, uint64_t* __restrict__ out)
+{
+    uint64_t acc = 0;
+    for (int i = threadIdx.x; i < n; i += 32) acc += partials[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if (threadIdx.x == 0) *out = acc;
+}
+
+// ---- light cache on the GPU (K4) ----
+// The chain is strictly serial (reference ethash.cpp:104-127): cache[i] needs cache[i-1].  One warp,
+// lane 0 does the permutation; it exists so that a host without spare cores can still build an epoch
+// entirely on the device.  See DESIGN.md for why the host build is the default.
+__global__ void light_cache_kernel(uint64_t* __restrict__ cache, uint32_t n, uint64_t s0, uint64_t s1, uint64_t s2,
+                                   uint64_t s3)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint64_t item[8];
+    {
+        const uint64_t in[4] = {s0, s1, s2, s3};
+        keccak512_32(in, item);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) cache[k] = item[k];
+    for (uint32_t i = 1; i < n; ++i) {
+        keccak512_64(item);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) cache[8 * (size_t)i + k] = item[k];
+    }
+    __threadfence();
+    for (int q = 0; q < 3; ++q) {
+        for (uint32_t i = 0; i < n; ++i) {
+            // cache[(i-1) mod n] is `item` from the previous step except at i == 0
+            const uint32_t v = (uint32_t)__ldcg(cache + 8 * (size_t)i) % n;
+            const uint32_t w = (n + i - 1) % n;
+            const uint64_t* a = cache + 8 * (size_t)v;
+            uint64_t x[8];
+            if (i == 0) {
+                const uint64_t* b = cache + 8 * (size_t)w;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = __ldcg(a + k) ^ __ldcg(b + k);
+            } else if (v == w) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = 0;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = __ldcg(a + k) ^ item[k];
+            }
+            keccak512_64(x);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                item[k] = x[k];
+                __stcg(cache + 8 * (size_t)i + k, x[k]);
+            }
+        }
+    }
+}
+}  // namespace
+
+int dag_generate(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256, void* out_dev,
+                 cudaStream_t s)
+{
+    if (count_item256 == 0) return NX_OK;
+    const uint64_t count512 = (uint64_t)count_item256 * 4;
+    if ((uint64_t)first_item256 * 4 + count512 > 0xffffffffull) {
+        set_error("dag_generate: item range exceeds 32-bit index space");
+        return NX_ERR_INVALID;
+    }
+    FastMod fm;
+    fm.d = (uint32_t)light_items;
+    fm.m = (uint32_t)((1ull << 32) / fm.d);
+    const uint32_t blocks = (uint32_t)((count512 + DAG_THREADS - 1) / DAG_THREADS);
+    dag_items_kernel<<<blocks, DAG_THREADS, 0, s>>>(static_cast<const uint4*>(light_dev), fm, first_item256 * 4u,
+                                                    (uint32_t)count512, static_cast<uint4*>(out_dev));
+    NX_CUDA(cudaGetLastError());
+    return NX_OK;
+}
+
+int light_cache_build_gpu(void* light_dev, int light_items, const uint8_t seed[32], cudaStream_t s)
+{
+    uint64_t w[4];
+    memcpy(w, seed, 32);
+    light_cache_kernel<<<1, 32, 0, s>>>(static_cast<uint64_t*>(light_dev), (uint32_t)light_items, w[0], w[1], w[2], w[3]);
+    NX_CUDA(cudaGetLastError());
+    return NX_OK;
+}
+
+int dag_checksum(const void* dag_dev, size_t n_words64, uint64_t* partials_dev, int n_partials, uint64_t* out_dev,
+                 cudaStream_t s)
+{
+    checksum_partial_kernel<<<n_partials, CSUM_THREADS, 0, s>>>(static_cast<const uint64_t*>(dag_dev), n_words64,
+                                                                 partials_dev);
+    NX_CUDA(cudaGetLastError());
+    checksum_final_kernel<<<1, 32, 0, s>>>(partials_dev, n_partials, out_dev);
+    NX_CUDA(cudaGetLastError());
+    return NX_OK;
+}
+
+}  // namespace nx

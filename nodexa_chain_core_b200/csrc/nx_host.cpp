@@ -1,0 +1,251 @@
+// Host-side pieces of the path: epoch geometry, Keccak sponges, the (inherently serial) light-cache
+// chain, the node glue (SHA256d header hash, compact target).  Product code; shares nothing with oracle/.
+#include "nx_internal.hpp"
+#include "nx_keccak.cuh"
+
+#include <cstdarg>
+#include <cstring>
+
+namespace nx
+{
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+void clear_error() { g_err[0] = 0; }
+
+// Original-Keccak sponge over arbitrary input (reference lib/keccak/keccak.c:46-101).
+static void sponge(uint8_t* out, size_t outlen, const uint8_t* data, size_t size)
+{
+    const size_t rate = 200 - 2 * outlen;
+    uint64_t st[25] = {0};
+    uint8_t block[200];
+    while (size >= rate) {
+        uint64_t w[25];
+        std::memcpy(w, data, rate);
+        for (size_t i = 0; i < rate / 8; ++i) st[i] ^= w[i];
+        keccakf1600(st);
+        data += rate;
+        size -= rate;
+    }
+    std::memset(block, 0, sizeof block);
+    if (size) std::memcpy(block, data, size);
+    block[size] ^= 0x01;
+    block[rate - 1] ^= 0x80;
+    uint64_t w[25];
+    std::memcpy(w, block, rate);
+    for (size_t i = 0; i < rate / 8; ++i) st[i] ^= w[i];
+    keccakf1600(st);
+    std::memcpy(out, st, outlen);
+}
+
+// reference lib/ethash/ethash.cpp:101-129 — 4*n dependent keccak512 calls; no parallelism to extract.
+void host_build_light_cache(uint8_t* cache, int n, const uint8_t seed[32])
+{
+    uint64_t* c = reinterpret_cast<uint64_t*>(cache);
+    uint64_t in[4], item[8];
+    std::memcpy(in, seed, 32);
+    keccak512_32(in, item);
+    std::memcpy(c, item, 64);
+    for (int i = 1; i < n; ++i) {
+        keccak512_64(item);
+        std::memcpy(c + 8 * (size_t)i, item, 64);
+    }
+    const uint32_t un = (uint32_t)n;
+    for (int q = 0; q < 3; ++q) {
+        for (int i = 0; i < n; ++i) {
+            const uint32_t v = (uint32_t)c[8 * (size_t)i] % un;
+            const uint32_t w = (uint32_t)(n + (i - 1)) % un;
+            const uint64_t *a = c + 8 * (size_t)v, *b = c + 8 * (size_t)w;
+            for (int k = 0; k < 8; ++k) item[k] = a[k] ^ b[k];
+            keccak512_64(item);
+            std::memcpy(c + 8 * (size_t)i, item, 64);
+        }
+    }
+}
+
+// ---- SHA-256 (FIPS 180-4) for the header hash; the node's own is src/crypto/sha256.cpp ----
+namespace
+{
+const uint32_t K256[64] = {
+    0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5, 0xd807aa98,
+    0x12835b01, 0x243185be, 0x550c7dc3, 0x72be5d74, 0x80deb1fe, 0x9bdc06a7, 0xc19bf174, 0xe49b69c1, 0xefbe4786,
+    0x0fc19dc6, 0x240ca1cc, 0x2de92c6f, 0x4a7484aa, 0x5cb0a9dc, 0x76f988da, 0x983e5152, 0xa831c66d, 0xb00327c8,
+    0xbf597fc7, 0xc6e00bf3, 0xd5a79147, 0x06ca6351, 0x14292967, 0x27b70a85, 0x2e1b2138, 0x4d2c6dfc, 0x53380d13,
+    0x650a7354, 0x766a0abb, 0x81c2c92e, 0x92722c85, 0xa2bfe8a1, 0xa81a664b, 0xc24b8b70, 0xc76c51a3, 0xd192e819,
+    0xd6990624, 0xf40e3585, 0x106aa070, 0x19a4c116, 0x1e376c08, 0x2748774c, 0x34b0bcb5, 0x391c0cb3, 0x4ed8aa4a,
+    0x5b9cca4f, 0x682e6ff3, 0x748f82ee, 0x78a5636f, 0x84c87814, 0x8cc70208, 0x90befffa, 0xa4506ceb, 0xbef9a3f7,
+    0xc67178f2};
+inline uint32_t rr(uint32_t x, int n) { return (x >> n) | (x << (32 - n)); }
+
+void sha256_block(uint32_t h[8], const uint8_t* p)
+{
+    uint32_t w[64];
+    for (int i = 0; i < 16; ++i)
+        w[i] = (uint32_t)p[4 * i] << 24 | (uint32_t)p[4 * i + 1] << 16 | (uint32_t)p[4 * i + 2] << 8 | p[4 * i + 3];
+    for (int i = 16; i < 64; ++i)
+        w[i] = w[i - 16] + (rr(w[i - 15], 7) ^ rr(w[i - 15], 18) ^ (w[i - 15] >> 3)) + w[i - 7] +
+               (rr(w[i - 2], 17) ^ rr(w[i - 2], 19) ^ (w[i - 2] >> 10));
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+    for (int i = 0; i < 64; ++i) {
+        const uint32_t t1 = hh + (rr(e, 6) ^ rr(e, 11) ^ rr(e, 25)) + ((e & f) ^ (~e & g)) + K256[i] + w[i];
+        const uint32_t t2 = (rr(a, 2) ^ rr(a, 13) ^ rr(a, 22)) + ((a & b) ^ (a & c) ^ (b & c));
+        hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
+    }
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
+}
+
+void sha256(const uint8_t* data, size_t n, uint8_t out[32])
+{
+    uint32_t h[8] = {0x6a09e667, 0xbb67ae85, 0x3c6ef372, 0xa54ff53a, 0x510e527f, 0x9b05688c, 0x1f83d9ab, 0x5be0cd19};
+    size_t off = 0;
+    for (; off + 64 <= n; off += 64) sha256_block(h, data + off);
+    uint8_t tail[128] = {0};
+    const size_t rem = n - off;
+    if (rem) std::memcpy(tail, data + off, rem);
+    tail[rem] = 0x80;
+    const size_t tl = rem + 9 <= 64 ? 64 : 128;
+    const uint64_t bits = (uint64_t)n * 8;
+    for (int i = 0; i < 8; ++i) tail[tl - 1 - i] = (uint8_t)(bits >> (8 * i));
+    sha256_block(h, tail);
+    if (tl == 128) sha256_block(h, tail + 64);
+    for (int i = 0; i < 8; ++i) {
+        out[4 * i] = (uint8_t)(h[i] >> 24);
+        out[4 * i + 1] = (uint8_t)(h[i] >> 16);
+        out[4 * i + 2] = (uint8_t)(h[i] >> 8);
+        out[4 * i + 3] = (uint8_t)h[i];
+    }
+}
+}  // namespace
+}  // namespace nx
+
+using namespace nx;
+
+extern "C" {
+
+const char* nx_last_error(void) { return g_err; }
+const char* nx_version(void) { return "nodexa-b200-pow 0.1 (KawPow/ProgPoW 0.9.4, sm_100a)"; }
+
+int nx_find_largest_prime(int upper_bound)
+{
+    if (upper_bound < 2) return 0;
+    if (upper_bound == 2) return 2;
+    int n = (upper_bound & 1) ? upper_bound : upper_bound - 1;
+    for (;; n -= 2) {
+        bool prime = true;
+        for (int64_t d = 3; d * d <= (int64_t)n; d += 2)
+            if (n % d == 0) {
+                prime = false;
+                break;
+            }
+        if (prime) return n;
+    }
+}
+
+int nx_light_cache_num_items(int epoch) { return nx_find_largest_prime((1 << 24) / 64 + epoch * ((1 << 17) / 64)); }
+int nx_full_dataset_num_items(int epoch) { return nx_find_largest_prime((1 << 30) / 128 + epoch * ((1 << 23) / 128)); }
+
+void nx_epoch_seed(int epoch, uint8_t out[32])
+{
+    uint64_t s[4] = {0, 0, 0, 0};
+    for (int i = 0; i < epoch; ++i) keccak256_32(s);
+    std::memcpy(out, s, 32);
+}
+
+int nx_find_epoch_number(const uint8_t seed[32])
+{
+    // The reference matches on the first 32-bit word only and gives up after 30000 epochs.
+    uint32_t want;
+    std::memcpy(&want, seed, 4);
+    uint64_t s[4] = {0, 0, 0, 0};
+    for (int i = 0; i < 30000; ++i) {
+        if ((uint32_t)s[0] == want) return i;
+        keccak256_32(s);
+    }
+    return -1;
+}
+
+void nx_keccakf1600(uint64_t state[25]) { keccakf1600(state); }
+void nx_keccakf800(uint32_t state[25]) { keccakf800(state); }
+void nx_keccak256(const uint8_t* data, size_t size, uint8_t out[32]) { sponge(out, 32, data, size); }
+void nx_keccak512(const uint8_t* data, size_t size, uint8_t out[64]) { sponge(out, 64, data, size); }
+
+void nx_kawpow_hash_no_verify(int block_number, const uint8_t header_hash[32], const uint8_t mix_hash[32],
+                              uint64_t nonce, uint8_t out[32])
+{
+    static const uint32_t pad[15] = {0x72, 0x41, 0x56, 0x45, 0x4E, 0x43, 0x4F, 0x49, 0x4E, 0x4B, 0x41, 0x57, 0x50, 0x4F, 0x57};
+    (void)block_number;
+    uint32_t st[25], carry[8];
+    std::memcpy(st, header_hash, 32);
+    st[8] = (uint32_t)nonce;
+    st[9] = (uint32_t)(nonce >> 32);
+    for (int i = 10; i < 25; ++i) st[i] = pad[i - 10];
+    keccakf800(st);
+    std::memcpy(carry, st, 32);
+    std::memcpy(st, carry, 32);
+    std::memcpy(st + 8, mix_hash, 32);
+    for (int i = 16; i < 25; ++i) st[i] = pad[i - 16];
+    keccakf800(st);
+    std::memcpy(out, st, 32);
+}
+
+void nx_sha256d(const uint8_t* data, size_t size, uint8_t out[32])
+{
+    uint8_t first[32];
+    sha256(data, size, first);
+    sha256(first, 32, out);
+}
+
+void nx_kawpow_header_hash(int32_t version, const uint8_t prev_block[32], const uint8_t merkle_root[32], uint32_t time,
+                           uint32_t bits, uint32_t height, uint8_t out[32])
+{
+    uint8_t in[80], d[32];
+    std::memcpy(in, &version, 4);
+    std::memcpy(in + 4, prev_block, 32);
+    std::memcpy(in + 36, merkle_root, 32);
+    std::memcpy(in + 68, &time, 4);
+    std::memcpy(in + 72, &bits, 4);
+    std::memcpy(in + 76, &height, 4);
+    nx_sha256d(in, 80, d);
+    for (int i = 0; i < 32; ++i) out[i] = d[31 - i];
+}
+
+int nx_compact_to_boundary(uint32_t bits, uint8_t out[32])
+{
+    const int size = (int)(bits >> 24);
+    uint32_t word = bits & 0x007fffffu;
+    uint8_t le[40] = {0};
+    if (size <= 3) {
+        word >>= 8 * (3 - size);
+        le[0] = (uint8_t)word;
+        le[1] = (uint8_t)(word >> 8);
+        le[2] = (uint8_t)(word >> 16);
+    } else if (size <= 34) {
+        le[size - 3] = (uint8_t)word;
+        le[size - 2] = (uint8_t)(word >> 8);
+        le[size - 1] = (uint8_t)(word >> 16);
+    }
+    const bool negative = word != 0 && (bits & 0x00800000u) != 0;
+    const bool overflow = word != 0 && ((size > 34) || (word > 0xff && size > 33) || (word > 0xffff && size > 32));
+    bool nonzero = false;
+    for (int i = 0; i < 32; ++i) {
+        out[i] = le[31 - i];
+        nonzero |= out[i] != 0;
+    }
+    return (!negative && !overflow && nonzero) ? 1 : 0;
+}
+
+int nx_check_proof_of_work(const uint8_t final_hash[32], uint32_t bits, const uint8_t pow_limit_be[32])
+{
+    uint8_t target[32];
+    if (!nx_compact_to_boundary(bits, target)) return 0;
+    if (pow_limit_be && std::memcmp(target, pow_limit_be, 32) > 0) return 0;
+    return std::memcmp(final_hash, target, 32) <= 0 ? 1 : 0;
+}
+
+}  // extern "C"

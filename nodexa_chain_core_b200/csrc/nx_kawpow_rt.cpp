@@ -1,0 +1,244 @@
+// Run-time side of the KawPow kernels: NVRTC compilation of the per-period program for sm_100a,
+// an in-process cache keyed by (device, prog_seed, DAG item count), and the launches.
+//
+// The period changes every 3 blocks (reference include/ethash/progpow.hpp:21), so compilation
+// (a few hundred ms) is kept off the hashing path by nx_kawpow_prepare() and by the cache; the
+// cubin can also be persisted in NX_PROGRAM_CACHE_DIR.
+#include "nx_internal.hpp"
+
+#include <dlfcn.h>
+#include <nvrtc.h>
+
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <map>
+#include <memory>
+#include <sstream>
+#include <tuple>
+
+namespace nx
+{
+namespace
+{
+// ---- the handful of driver-API entry points we need, resolved lazily from libcuda.so.1 so that
+//      the library itself loads (and its symbols can be inspected) on a machine without a driver ----
+typedef int CUresult_;
+typedef struct CUmod_st* CUmodule_;
+typedef struct CUfunc_st* CUfunction_;
+struct Driver
+{
+    void* lib = nullptr;
+    CUresult_ (*ModuleLoadData)(CUmodule_*, const void*) = nullptr;
+    CUresult_ (*ModuleUnload)(CUmodule_) = nullptr;
+    CUresult_ (*ModuleGetFunction)(CUfunction_*, CUmodule_, const char*) = nullptr;
+    CUresult_ (*LaunchKernel)(CUfunction_, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned,
+                              void* /*CUstream*/, void**, void**) = nullptr;
+    CUresult_ (*GetErrorString)(CUresult_, const char**) = nullptr;
+    CUresult_ (*FuncSetAttribute)(CUfunction_, int, int) = nullptr;
+    CUresult_ (*FuncGetAttribute)(int*, int, CUfunction_) = nullptr;
+    bool ok = false;
+};
+
+Driver& driver()
+{
+    static Driver d;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        d.lib = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+        if (!d.lib) return;
+#define NX_SYM(field, name) *(void**)(&d.field) = dlsym(d.lib, name)
+        NX_SYM(ModuleLoadData, "cuModuleLoadData");
+        NX_SYM(ModuleUnload, "cuModuleUnload");
+        NX_SYM(ModuleGetFunction, "cuModuleGetFunction");
+        NX_SYM(LaunchKernel, "cuLaunchKernel");
+        NX_SYM(GetErrorString, "cuGetErrorString");
+        NX_SYM(FuncSetAttribute, "cuFuncSetAttribute");
+        NX_SYM(FuncGetAttribute, "cuFuncGetAttribute");
+#undef NX_SYM
+        d.ok = d.ModuleLoadData && d.ModuleUnload && d.ModuleGetFunction && d.LaunchKernel && d.GetErrorString;
+    });
+    return d;
+}
+
+const char* cu_err(CUresult_ r)
+{
+    const char* s = nullptr;
+    if (driver().GetErrorString) driver().GetErrorString(r, &s);
+    return s ? s : "unknown driver error";
+}
+
+std::string cache_path(uint64_t prog_seed, uint32_t dag_items, const char* arch)
+{
+    const char* dir = std::getenv("NX_PROGRAM_CACHE_DIR");
+    if (!dir || !*dir) return "";
+    std::ostringstream s;
+    s << dir << "/kawpow_" << arch << "_" << prog_seed << "_" << dag_items << "_v1.cubin";
+    return s.str();
+}
+}  // namespace
+
+struct KawpowProgram
+{
+    int device = 0;
+    uint64_t prog_seed = 0;
+    uint32_t dag_items = 0;
+    CUmodule_ module = nullptr;
+    CUfunction_ fn_hash = nullptr, fn_search = nullptr;
+    double compile_ms = 0;
+    int regs_hash = 0, regs_search = 0;
+    ~KawpowProgram();
+};
+
+KawpowProgram::~KawpowProgram()
+{
+    if (module && driver().ModuleUnload) driver().ModuleUnload(module);
+}
+
+namespace
+{
+std::mutex g_cache_mu;
+std::map<std::tuple<int, uint64_t, uint32_t>, std::shared_ptr<KawpowProgram>> g_cache;
+
+int compile_cubin(uint64_t prog_seed, uint32_t dag_items, std::vector<char>& cubin, std::string& log)
+{
+    const std::string src = kawpow_source(prog_seed, dag_items);
+    nvrtcProgram prog = nullptr;
+    if (nvrtcCreateProgram(&prog, src.c_str(), "nx_kawpow_period.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS) {
+        set_error("nvrtcCreateProgram failed");
+        return NX_ERR_NVRTC;
+    }
+    const char* arch_env = std::getenv("NX_KAWPOW_ARCH");
+    const std::string arch = std::string("--gpu-architecture=") + (arch_env && *arch_env ? arch_env : "sm_100a");
+    std::vector<const char*> opts = {arch.c_str(), "--std=c++17", "-lineinfo", "--extra-device-vectorization"};
+    std::vector<std::string> extra;
+    if (const char* e = std::getenv("NX_KAWPOW_NVRTC_FLAGS")) {  // space separated, for experiments
+        std::istringstream is(e);
+        std::string tok;
+        while (is >> tok) extra.push_back(tok);
+        for (auto& t : extra) opts.push_back(t.c_str());
+    }
+    const nvrtcResult rc = nvrtcCompileProgram(prog, (int)opts.size(), opts.data());
+    size_t log_size = 0;
+    nvrtcGetProgramLogSize(prog, &log_size);
+    if (log_size > 1) {
+        log.resize(log_size);
+        nvrtcGetProgramLog(prog, &log[0]);
+    }
+    if (rc != NVRTC_SUCCESS) {
+        set_error("NVRTC: %s: %.400s", nvrtcGetErrorString(rc), log.c_str());
+        nvrtcDestroyProgram(&prog);
+        return NX_ERR_NVRTC;
+    }
+    size_t n = 0;
+    if (nvrtcGetCUBINSize(prog, &n) != NVRTC_SUCCESS || n == 0) {
+        set_error("NVRTC produced no cubin (arch %s)", arch.c_str());
+        nvrtcDestroyProgram(&prog);
+        return NX_ERR_NVRTC;
+    }
+    cubin.resize(n);
+    nvrtcGetCUBIN(prog, cubin.data());
+    nvrtcDestroyProgram(&prog);
+    return NX_OK;
+}
+}  // namespace
+
+// Exposed for tests and tools: compile only (no device needed) and hand back the cubin bytes.
+int kawpow_compile_only(uint64_t prog_seed, uint32_t dag_items, std::vector<char>& cubin, std::string& log)
+{
+    return compile_cubin(prog_seed, dag_items, cubin, log);
+}
+
+int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<KawpowProgram>* out)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    const auto key = std::make_tuple(device, prog_seed, dag_items);
+    auto it = g_cache.find(key);
+    if (it != g_cache.end()) {
+        *out = it->second;
+        return NX_OK;
+    }
+    Driver& d = driver();
+    if (!d.ok) {
+        set_error("libcuda.so.1 not available: a CUDA driver is required (no CPU fallback)");
+        return NX_ERR_CUDA;
+    }
+    NX_CUDA(cudaSetDevice(device));
+    NX_CUDA(cudaFree(nullptr));  // make sure the primary context exists and is current
+
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<char> cubin;
+    const char* arch_env = std::getenv("NX_KAWPOW_ARCH");
+    const std::string path = cache_path(prog_seed, dag_items, arch_env && *arch_env ? arch_env : "sm_100a");
+    if (!path.empty()) {
+        std::ifstream f(path, std::ios::binary);
+        if (f) cubin.assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
+    }
+    if (cubin.empty()) {
+        std::string log;
+        const int rc = compile_cubin(prog_seed, dag_items, cubin, log);
+        if (rc != NX_OK) return rc;
+        if (!path.empty()) {
+            std::ofstream f(path, std::ios::binary);
+            f.write(cubin.data(), (std::streamsize)cubin.size());
+        }
+    }
+    std::shared_ptr<KawpowProgram> p(new KawpowProgram);
+    p->device = device;
+    p->prog_seed = prog_seed;
+    p->dag_items = dag_items;
+    CUresult_ r = d.ModuleLoadData(&p->module, cubin.data());
+    if (r != 0) {
+        set_error("cuModuleLoadData failed: %s", cu_err(r));
+        return NX_ERR_CUDA;
+    }
+    if ((r = d.ModuleGetFunction(&p->fn_hash, p->module, "nx_kawpow_hash_kernel")) != 0 ||
+        (r = d.ModuleGetFunction(&p->fn_search, p->module, "nx_kawpow_search_kernel")) != 0) {
+        set_error("cuModuleGetFunction failed: %s", cu_err(r));
+        return NX_ERR_CUDA;
+    }
+    if (d.FuncGetAttribute) {
+        d.FuncGetAttribute(&p->regs_hash, 4 /*CU_FUNC_ATTRIBUTE_NUM_REGS*/, p->fn_hash);
+        d.FuncGetAttribute(&p->regs_search, 4, p->fn_search);
+    }
+    p->compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (std::getenv("NX_VERBOSE"))
+        fprintf(stderr, "[nx] kawpow program seed=%llu items=%u: %.1f ms, regs hash=%d search=%d\n",
+                (unsigned long long)prog_seed, dag_items, p->compile_ms, p->regs_hash, p->regs_search);
+    // keep the cache bounded: a node only needs the current and the next period.  Evicted programs
+    // are unloaded when their last user lets go of the shared_ptr.
+    if (g_cache.size() >= 32) g_cache.clear();
+    *out = p;
+    g_cache[key] = p;
+    return NX_OK;
+}
+
+static int launch(CUfunction_ fn, const void* dag, const KawpowJob& job, void* third, cudaStream_t s)
+{
+    if (job.count == 0) return NX_OK;
+    const uint64_t blocks = (job.count + KAWPOW_THREADS - 1) / KAWPOW_THREADS;
+    if (blocks > 0x7fffffffull) {
+        set_error("kawpow launch: batch of %llu nonces is too large for one grid", (unsigned long long)job.count);
+        return NX_ERR_INVALID;
+    }
+    void* args[3] = {(void*)&dag, (void*)&job, (void*)&third};
+    const CUresult_ r = driver().LaunchKernel(fn, (unsigned)blocks, 1, 1, KAWPOW_THREADS, 1, 1, 0, (void*)s, args, nullptr);
+    if (r != 0) {
+        set_error("cuLaunchKernel failed: %s", cu_err(r));
+        return NX_ERR_CUDA;
+    }
+    return NX_OK;
+}
+
+int kawpow_launch_hash(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* out_dev, cudaStream_t s)
+{
+    return launch(p->fn_hash, dag, job, out_dev, s);
+}
+
+int kawpow_launch_search(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* found_min_dev, cudaStream_t s)
+{
+    return launch(p->fn_search, dag, job, found_min_dev, s);
+}
+
+}  // namespace nx

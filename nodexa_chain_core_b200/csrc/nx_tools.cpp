@@ -1,0 +1,54 @@
+// Introspection entry points used by the tests and by tools/ (no device needed):
+// the generated program text and an NVRTC compile that stops at the cubin.
+#include "nx_internal.hpp"
+
+#include <cstring>
+
+using namespace nx;
+
+extern "C" {
+
+// Writes the generated CUDA text for (prog_seed, dag_items) into buf (NUL-terminated, truncated to
+// cap); returns the full length.  with_skeleton=0 gives only the two NX_ROUND_* macros.
+size_t nx_kawpow_program_source(uint64_t prog_seed, uint32_t dag_items_256, int with_skeleton, char* buf, size_t cap)
+{
+    const std::string s = with_skeleton ? kawpow_source(prog_seed, dag_items_256) : kawpow_program_text(prog_seed);
+    if (buf && cap) {
+        const size_t n = s.size() < cap - 1 ? s.size() : cap - 1;
+        std::memcpy(buf, s.data(), n);
+        buf[n] = 0;
+    }
+    return s.size();
+}
+
+// Flat op list of the period program: ops[i] = {kind, src1, src2, dst, sel_math, sel_merge}; returns count (33).
+int nx_kawpow_program_ops(uint64_t prog_seed, uint32_t (*ops)[6], int cap)
+{
+    const std::vector<ProgramOp> v = kawpow_program(prog_seed);
+    int n = 0;
+    for (const ProgramOp& op : v) {
+        if (n >= cap) break;
+        ops[n][0] = (uint32_t)op.kind;
+        ops[n][1] = op.src1;
+        ops[n][2] = op.src2;
+        ops[n][3] = op.dst;
+        ops[n][4] = op.sel_math;
+        ops[n][5] = op.sel_merge;
+        ++n;
+    }
+    return n;
+}
+
+// NVRTC-compile the period program for sm_100a without touching a device; the cubin is copied to
+// buf when it fits.  Returns the cubin size, or a negative nx_status.
+long nx_kawpow_compile_cubin(uint64_t prog_seed, uint32_t dag_items_256, char* buf, size_t cap)
+{
+    std::vector<char> cubin;
+    std::string log;
+    const int rc = kawpow_compile_only(prog_seed, dag_items_256, cubin, log);
+    if (rc != NX_OK) return rc;
+    if (buf && cap >= cubin.size()) std::memcpy(buf, cubin.data(), cubin.size());
+    return (long)cubin.size();
+}
+
+}  // extern "C"

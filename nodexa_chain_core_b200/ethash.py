@@ -1,0 +1,180 @@
+"""Mirror of the reference's `ethash::` namespace for the KawPow path
+(src/crypto/ethash/include/ethash/ethash.hpp:24-172, ethash.h:20-131)."""
+from __future__ import annotations
+
+import ctypes as C
+
+from ._lib import check, inb, lib, outb
+
+epoch_length = 7500  # ethash.h:29
+light_cache_item_size = 64
+full_dataset_item_size = 128
+
+
+def get_epoch_number(block_number: int) -> int:
+    """ethash.hpp:75-78"""
+    return block_number // epoch_length if block_number else 0
+
+
+def calculate_light_cache_num_items(epoch_number: int) -> int:
+    return lib.nx_light_cache_num_items(epoch_number)
+
+
+def calculate_full_dataset_num_items(epoch_number: int) -> int:
+    return lib.nx_full_dataset_num_items(epoch_number)
+
+
+def calculate_epoch_seed(epoch_number: int) -> bytes:
+    o = outb(32)
+    lib.nx_epoch_seed(epoch_number, o)
+    return bytes(o)
+
+
+def find_epoch_number(seed: bytes) -> int:
+    """ethash.cpp:57-97; -1 when the seed is not found within 30000 epochs."""
+    return lib.nx_find_epoch_number(inb(seed))
+
+
+def keccak256(data: bytes) -> bytes:
+    o = outb(32)
+    lib.nx_keccak256(inb(data) if data else outb(1), len(data), o)
+    return bytes(o)
+
+
+def keccak512(data: bytes) -> bytes:
+    o = outb(64)
+    lib.nx_keccak512(inb(data) if data else outb(1), len(data), o)
+    return bytes(o)
+
+
+class EpochContext:
+    """Owns one epoch's light cache, L1 cache and full DAG on one GPU.
+
+    Public attributes follow struct ethash_epoch_context (ethash.h:35-42): epoch_number,
+    light_cache_num_items, light_cache, l1_cache, full_dataset_num_items.  The reference
+    distinguishes a light and a full context; on B200 both hold the resident DAG.
+    """
+
+    def __init__(self, epoch_number: int, device: int = 0, rank: int = 0, world: int = 1):
+        h = C.c_void_p()
+        if world == 1:
+            check(lib.nx_epoch_create(epoch_number, device, C.byref(h)))
+        else:
+            check(lib.nx_epoch_create_sharded(epoch_number, device, rank, world, C.byref(h)))
+        self._h = h
+        self.rank, self.world = rank, world
+
+    # -- reference-visible fields --
+    @property
+    def epoch_number(self) -> int:
+        return lib.nx_epoch_number(self._h)
+
+    @property
+    def light_cache_num_items(self) -> int:
+        return lib.nx_epoch_light_items(self._h)
+
+    @property
+    def full_dataset_num_items(self) -> int:
+        return lib.nx_epoch_dataset_items(self._h)
+
+    @property
+    def light_cache(self) -> bytes:
+        return C.string_at(lib.nx_epoch_light_cache(self._h), self.light_cache_num_items * 64)
+
+    @property
+    def l1_cache(self):
+        p = lib.nx_epoch_l1_cache(self._h)
+        return [p[i] for i in range(4096)]
+
+    # -- device side --
+    @property
+    def device(self) -> int:
+        return lib.nx_epoch_device(self._h)
+
+    @property
+    def dag_ptr(self) -> int:
+        return lib.nx_epoch_dag_ptr(self._h)
+
+    @property
+    def dag_bytes(self) -> int:
+        return lib.nx_epoch_dag_bytes(self._h)
+
+    @property
+    def dag_padded_bytes(self) -> int:
+        return lib.nx_epoch_dag_padded_bytes(self._h)
+
+    @property
+    def dag_share_bytes(self) -> int:
+        return lib.nx_epoch_dag_share_bytes(self._h)
+
+    @property
+    def dag_num_items(self) -> int:
+        """256-byte items addressable by KawPow = full_dataset_num_items // 2 (progpow.cpp:182)."""
+        return self.dag_bytes // 256
+
+    def build_times_ms(self):
+        a, b = C.c_double(), C.c_double()
+        lib.nx_epoch_build_times(self._h, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def finalize(self):
+        """After the caller's in-place all-gather of a sharded DAG."""
+        check(lib.nx_epoch_finalize(self._h))
+
+    def dag_tensor(self):
+        """The padded DAG as a torch uint8 CUDA tensor aliasing the library's buffer (for NCCL)."""
+        import torch
+
+        class _Arr:
+            pass
+
+        a = _Arr()
+        a.__cuda_array_interface__ = {"shape": (self.dag_padded_bytes,), "typestr": "|u1",
+                                      "data": (self.dag_ptr, False), "version": 2}
+        a._keepalive = self
+        return torch.as_tensor(a, device=f"cuda:{self.device}")
+
+    def read_items(self, first: int, count: int) -> bytes:
+        o = outb(256 * count)
+        check(lib.nx_dag_read_items(self._h, first, count, o))
+        return bytes(o)
+
+    def generate_range(self, first: int, count: int, out_device_ptr: int):
+        check(lib.nx_dag_generate_range(self._h, first, count, C.c_void_p(out_device_ptr)))
+
+    def checksum(self) -> int:
+        v = C.c_uint64()
+        check(lib.nx_dag_checksum(self._h, C.byref(v)))
+        return v.value
+
+    def last_timing(self):
+        ms, n = C.c_float(), C.c_int()
+        lib.nx_kawpow_last_timing(self._h, C.byref(ms), C.byref(n))
+        return ms.value, n.value
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.nx_epoch_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def create_epoch_context(epoch_number: int, device: int = 0) -> EpochContext:
+    """ethash.hpp:112-115 / ethash.cpp:395-398"""
+    return EpochContext(epoch_number, device)
+
+
+def create_epoch_context_full(epoch_number: int, device: int = 0) -> EpochContext:
+    """ethash.hpp:117-120 / ethash.cpp:400-403"""
+    return EpochContext(epoch_number, device)

@@ -1,0 +1,347 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes bindings for the CPU oracle.
+
+`Oracle`  -> oracle/libnxoracle.so  (our plain-C restatement, oracle/nx_oracle.c; kind "port")
+`Ref`     -> oracle/_ref/libnxref.so (the reference's own sources compiled in place by
+             `make -C oracle ref`; kind "reference").  Present only where it was built
+             (this container; it travels to the GPU box as a prebuilt .so).
+
+Nothing in nodexa_chain_core_b200/ imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "libnxoracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libnxref.so")
+
+u8p = C.POINTER(C.c_uint8)
+
+
+def build_oracle() -> str:
+    subprocess.check_call(["make", "-s", "-C", HERE, "oracle"])
+    return ORACLE_SO
+
+
+def build_ref() -> str | None:
+    """Compile the reference TUs where they lie (only where /root/reference exists)."""
+    if not os.path.isdir("/root/reference/src/crypto/ethash"):
+        return REF_SO if os.path.exists(REF_SO) else None
+    subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
+    return REF_SO
+
+
+def _buf(n):
+    return (C.c_uint8 * n)()
+
+
+def _in(b: bytes):
+    return (C.c_uint8 * len(b)).from_buffer_copy(b)
+
+
+class _Ctx(C.Structure):
+    _fields_ = [("epoch", C.c_int), ("light_items", C.c_int), ("dataset_items", C.c_int),
+                ("light", C.c_void_p), ("l1", C.c_uint32 * 4096), ("dag", C.c_void_p)]
+
+
+class Oracle:
+    kind = "port"
+
+    def __init__(self):
+        if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
+                os.path.join(HERE, "nx_oracle.c")):
+            build_oracle()
+        L = self.L = C.CDLL(ORACLE_SO)
+        L.nxo_ctx_create.restype = C.POINTER(_Ctx)
+        L.nxo_ctx_create.argtypes = [C.c_int]
+        L.nxo_ctx_destroy.argtypes = [C.POINTER(_Ctx)]
+        L.nxo_ctx_set_dag.argtypes = [C.POINTER(_Ctx), C.c_void_p]
+        L.nxo_kawpow_hash.argtypes = [C.POINTER(_Ctx), C.c_int, u8p, C.c_uint64, u8p, u8p]
+        L.nxo_kawpow_hash_range.argtypes = [C.POINTER(_Ctx), C.c_int, u8p, C.c_uint64, C.c_uint64, u8p, C.c_int]
+        L.nxo_kawpow_verify.argtypes = [C.POINTER(_Ctx), C.c_int, u8p, u8p, C.c_uint64, u8p]
+        L.nxo_kawpow_hash_no_verify.argtypes = [C.c_int, u8p, u8p, C.c_uint64, u8p]
+        L.nxo_kawpow_search_mt.argtypes = [C.POINTER(_Ctx), C.c_int, u8p, u8p, C.c_uint64, C.c_uint64,
+                                           C.POINTER(C.c_uint64), u8p, u8p, C.c_int]
+        L.nxo_kawpow_program.argtypes = [C.c_uint64, C.POINTER(C.c_uint32 * 6)]
+        L.nxo_dataset_item_512.argtypes = [C.POINTER(_Ctx), C.c_int64, u8p]
+        L.nxo_dataset_item_2048.argtypes = [C.POINTER(_Ctx), C.c_uint32, u8p]
+        L.nxo_dataset_items_2048.argtypes = [C.POINTER(_Ctx), C.c_uint32, C.c_uint32, u8p, C.c_int]
+        L.nxo_ethash_hash.argtypes = [C.POINTER(_Ctx), u8p, C.c_uint64, u8p, u8p]
+        L.nxo_ethash_verify_final.argtypes = [u8p, u8p, C.c_uint64, u8p]
+        L.nxo_epoch_seed.argtypes = [C.c_int, u8p]
+        L.nxo_find_epoch_number.argtypes = [u8p]
+        L.nxo_keccak256.argtypes = [u8p, C.c_size_t, u8p]
+        L.nxo_keccak512.argtypes = [u8p, C.c_size_t, u8p]
+        L.nxo_keccakf800.argtypes = [C.POINTER(C.c_uint32)]
+        L.nxo_keccakf1600.argtypes = [C.POINTER(C.c_uint64)]
+        L.nxo_sha256.argtypes = [u8p, C.c_size_t, u8p]
+        L.nxo_kawpow_header_hash.argtypes = [C.c_int32, u8p, u8p, C.c_uint32, C.c_uint32, C.c_uint32, u8p]
+        L.nxo_compact_to_boundary.argtypes = [C.c_uint32, u8p]
+        L.nxo_less_or_equal.argtypes = [u8p, u8p]
+        L.nxo_build_light_cache.argtypes = [u8p, C.c_int, u8p]
+        self._ctx = {}
+
+    # -- contexts are cached per epoch (light cache build is ~1 s) --
+    def ctx(self, epoch: int):
+        if epoch not in self._ctx:
+            c = self.L.nxo_ctx_create(epoch)
+            if not c:
+                raise MemoryError("oracle context")
+            self._ctx[epoch] = c
+        return self._ctx[epoch]
+
+    def light_items(self, epoch):
+        return self.L.nxo_light_cache_num_items(epoch)
+
+    def dataset_items(self, epoch):
+        return self.L.nxo_full_dataset_num_items(epoch)
+
+    def light_cache(self, epoch) -> bytes:
+        c = self.ctx(epoch)
+        return C.string_at(c.contents.light, c.contents.light_items * 64)
+
+    def l1(self, epoch):
+        return list(self.ctx(epoch).contents.l1)
+
+    def set_dag(self, epoch, ptr):
+        self.L.nxo_ctx_set_dag(self.ctx(epoch), ptr)
+
+    def epoch_seed(self, epoch) -> bytes:
+        o = _buf(32)
+        self.L.nxo_epoch_seed(epoch, o)
+        return bytes(o)
+
+    def find_epoch_number(self, seed: bytes) -> int:
+        return self.L.nxo_find_epoch_number(_in(seed))
+
+    def keccak256(self, d: bytes) -> bytes:
+        o = _buf(32)
+        self.L.nxo_keccak256(_in(d) if d else _buf(1), len(d), o)
+        return bytes(o)
+
+    def keccak512(self, d: bytes) -> bytes:
+        o = _buf(64)
+        self.L.nxo_keccak512(_in(d) if d else _buf(1), len(d), o)
+        return bytes(o)
+
+    def keccakf800(self, words):
+        a = (C.c_uint32 * 25)(*words)
+        self.L.nxo_keccakf800(a)
+        return list(a)
+
+    def keccakf1600(self, words):
+        a = (C.c_uint64 * 25)(*words)
+        self.L.nxo_keccakf1600(a)
+        return list(a)
+
+    def kawpow_hash(self, epoch, height, header: bytes, nonce: int):
+        f, m = _buf(32), _buf(32)
+        self.L.nxo_kawpow_hash(self.ctx(epoch), height, _in(header), nonce, f, m)
+        return bytes(f), bytes(m)
+
+    def kawpow_hash_range(self, epoch, height, header: bytes, start: int, count: int, threads: int = 0) -> bytes:
+        out = _buf(64 * count)
+        self.L.nxo_kawpow_hash_range(self.ctx(epoch), height, _in(header), start, count, out,
+                                     threads or os.cpu_count() or 1)
+        return bytes(out)
+
+    def kawpow_verify(self, epoch, height, header, mix, nonce, boundary) -> bool:
+        return bool(self.L.nxo_kawpow_verify(self.ctx(epoch), height, _in(header), _in(mix), nonce, _in(boundary)))
+
+    def kawpow_hash_no_verify(self, height, header, mix, nonce) -> bytes:
+        o = _buf(32)
+        self.L.nxo_kawpow_hash_no_verify(height, _in(header), _in(mix), nonce, o)
+        return bytes(o)
+
+    def kawpow_search(self, epoch, height, header, boundary, start, iterations, threads: int = 0):
+        n = C.c_uint64(0)
+        f, m = _buf(32), _buf(32)
+        found = self.L.nxo_kawpow_search_mt(self.ctx(epoch), height, _in(header), _in(boundary), start, iterations,
+                                            C.byref(n), f, m, threads or os.cpu_count() or 1)
+        return bool(found), n.value, bytes(f), bytes(m)
+
+    def kawpow_program(self, prog_seed: int):
+        ops = ((C.c_uint32 * 6) * 33)()
+        n = self.L.nxo_kawpow_program(prog_seed, ops)
+        return [tuple(ops[i]) for i in range(n)]
+
+    def dataset_item_512(self, epoch, index) -> bytes:
+        o = _buf(64)
+        self.L.nxo_dataset_item_512(self.ctx(epoch), index, o)
+        return bytes(o)
+
+    def dataset_item_2048(self, epoch, index) -> bytes:
+        o = _buf(256)
+        self.L.nxo_dataset_item_2048(self.ctx(epoch), index, o)
+        return bytes(o)
+
+    def dataset_items_2048(self, epoch, first, count, threads: int = 0) -> bytes:
+        o = _buf(256 * count)
+        self.L.nxo_dataset_items_2048(self.ctx(epoch), first, count, o, threads or os.cpu_count() or 1)
+        return bytes(o)
+
+    def ethash_hash(self, epoch, header, nonce):
+        f, m = _buf(32), _buf(32)
+        self.L.nxo_ethash_hash(self.ctx(epoch), _in(header), nonce, f, m)
+        return bytes(f), bytes(m)
+
+    def ethash_verify_final(self, header, mix, nonce, boundary) -> bool:
+        return bool(self.L.nxo_ethash_verify_final(_in(header), _in(mix), nonce, _in(boundary)))
+
+    def sha256(self, d: bytes) -> bytes:
+        o = _buf(32)
+        self.L.nxo_sha256(_in(d) if d else _buf(1), len(d), o)
+        return bytes(o)
+
+    def kawpow_header_hash(self, version, prev, merkle, time, bits, height) -> bytes:
+        o = _buf(32)
+        self.L.nxo_kawpow_header_hash(version, _in(prev), _in(merkle), time, bits, height, o)
+        return bytes(o)
+
+    def compact_to_boundary(self, bits):
+        o = _buf(32)
+        ok = self.L.nxo_compact_to_boundary(bits, o)
+        return bool(ok), bytes(o)
+
+    def less_or_equal(self, a, b) -> bool:
+        return bool(self.L.nxo_less_or_equal(_in(a), _in(b)))
+
+
+class Ref:
+    """The reference's own compiled code (oracle/_ref/libnxref.so)."""
+    kind = "reference"
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(REF_SO)
+
+    def __init__(self):
+        if not os.path.exists(REF_SO):
+            if build_ref() is None or not os.path.exists(REF_SO):
+                raise FileNotFoundError(REF_SO)
+        L = self.L = C.CDLL(REF_SO)
+        vp = C.c_void_p
+        L.nxref_ctx_create.restype = vp
+        L.nxref_ctx_create.argtypes = [C.c_int]
+        L.nxref_ctx_destroy.argtypes = [vp]
+        L.nxref_ctx_light_items.argtypes = [vp]
+        L.nxref_ctx_dataset_items.argtypes = [vp]
+        L.nxref_ctx_light_cache.restype = vp
+        L.nxref_ctx_light_cache.argtypes = [vp]
+        L.nxref_ctx_l1.restype = C.POINTER(C.c_uint32)
+        L.nxref_ctx_l1.argtypes = [vp]
+        L.nxref_kawpow_hash.argtypes = [vp, C.c_int, u8p, C.c_uint64, u8p, u8p]
+        L.nxref_kawpow_hash_range.argtypes = [vp, C.c_int, u8p, C.c_uint64, C.c_uint64, u8p, C.c_int]
+        L.nxref_kawpow_verify.argtypes = [vp, C.c_int, u8p, u8p, C.c_uint64, u8p]
+        L.nxref_kawpow_hash_no_verify.argtypes = [C.c_int, u8p, u8p, C.c_uint64, u8p]
+        L.nxref_kawpow_search_light.argtypes = [vp, C.c_int, u8p, u8p, C.c_uint64, C.c_uint64,
+                                                C.POINTER(C.c_uint64), u8p, u8p]
+        L.nxref_dataset_item_512.argtypes = [vp, C.c_int64, u8p]
+        L.nxref_dataset_item_2048.argtypes = [vp, C.c_uint32, u8p]
+        L.nxref_dataset_items_2048.argtypes = [vp, C.c_uint32, C.c_uint32, u8p, C.c_int]
+        L.nxref_ethash_hash.argtypes = [vp, u8p, C.c_uint64, u8p, u8p]
+        L.nxref_epoch_seed.argtypes = [C.c_int, u8p]
+        L.nxref_find_epoch_number.argtypes = [u8p]
+        L.nxref_keccak256.argtypes = [u8p, C.c_size_t, u8p]
+        L.nxref_keccak512.argtypes = [u8p, C.c_size_t, u8p]
+        L.nxref_keccakf800.argtypes = [C.POINTER(C.c_uint32)]
+        L.nxref_keccakf1600.argtypes = [C.POINTER(C.c_uint64)]
+        self._ctx = {}
+
+    def ctx(self, epoch):
+        if epoch not in self._ctx:
+            c = self.L.nxref_ctx_create(epoch)
+            if not c:
+                raise MemoryError("reference context")
+            self._ctx[epoch] = c
+        return self._ctx[epoch]
+
+    def light_items(self, epoch):
+        return self.L.nxref_light_cache_num_items(epoch)
+
+    def dataset_items(self, epoch):
+        return self.L.nxref_full_dataset_num_items(epoch)
+
+    def light_cache(self, epoch) -> bytes:
+        c = self.ctx(epoch)
+        return C.string_at(self.L.nxref_ctx_light_cache(c), self.L.nxref_ctx_light_items(c) * 64)
+
+    def l1(self, epoch):
+        p = self.L.nxref_ctx_l1(self.ctx(epoch))
+        return [p[i] for i in range(4096)]
+
+    def epoch_seed(self, epoch) -> bytes:
+        o = _buf(32)
+        self.L.nxref_epoch_seed(epoch, o)
+        return bytes(o)
+
+    def find_epoch_number(self, seed: bytes) -> int:
+        return self.L.nxref_find_epoch_number(_in(seed))
+
+    def keccak256(self, d: bytes) -> bytes:
+        o = _buf(32)
+        self.L.nxref_keccak256(_in(d) if d else _buf(1), len(d), o)
+        return bytes(o)
+
+    def keccak512(self, d: bytes) -> bytes:
+        o = _buf(64)
+        self.L.nxref_keccak512(_in(d) if d else _buf(1), len(d), o)
+        return bytes(o)
+
+    def keccakf800(self, words):
+        a = (C.c_uint32 * 25)(*words)
+        self.L.nxref_keccakf800(a)
+        return list(a)
+
+    def keccakf1600(self, words):
+        a = (C.c_uint64 * 25)(*words)
+        self.L.nxref_keccakf1600(a)
+        return list(a)
+
+    def kawpow_hash(self, epoch, height, header, nonce):
+        f, m = _buf(32), _buf(32)
+        self.L.nxref_kawpow_hash(self.ctx(epoch), height, _in(header), nonce, f, m)
+        return bytes(f), bytes(m)
+
+    def kawpow_hash_range(self, epoch, height, header, start, count, threads: int = 0) -> bytes:
+        out = _buf(64 * count)
+        self.L.nxref_kawpow_hash_range(self.ctx(epoch), height, _in(header), start, count, out,
+                                       threads or os.cpu_count() or 1)
+        return bytes(out)
+
+    def kawpow_verify(self, epoch, height, header, mix, nonce, boundary) -> bool:
+        return bool(self.L.nxref_kawpow_verify(self.ctx(epoch), height, _in(header), _in(mix), nonce, _in(boundary)))
+
+    def kawpow_hash_no_verify(self, height, header, mix, nonce) -> bytes:
+        o = _buf(32)
+        self.L.nxref_kawpow_hash_no_verify(height, _in(header), _in(mix), nonce, o)
+        return bytes(o)
+
+    def kawpow_search(self, epoch, height, header, boundary, start, iterations, threads: int = 0):
+        n = C.c_uint64(0)
+        f, m = _buf(32), _buf(32)
+        found = self.L.nxref_kawpow_search_light(self.ctx(epoch), height, _in(header), _in(boundary), start,
+                                                 iterations, C.byref(n), f, m)
+        return bool(found), n.value, bytes(f), bytes(m)
+
+    def dataset_item_512(self, epoch, index) -> bytes:
+        o = _buf(64)
+        self.L.nxref_dataset_item_512(self.ctx(epoch), index, o)
+        return bytes(o)
+
+    def dataset_item_2048(self, epoch, index) -> bytes:
+        o = _buf(256)
+        self.L.nxref_dataset_item_2048(self.ctx(epoch), index, o)
+        return bytes(o)
+
+    def dataset_items_2048(self, epoch, first, count, threads: int = 0) -> bytes:
+        o = _buf(256 * count)
+        self.L.nxref_dataset_items_2048(self.ctx(epoch), first, count, o, threads or os.cpu_count() or 1)
+        return bytes(o)
+
+    def ethash_hash(self, epoch, header, nonce):
+        f, m = _buf(32), _buf(32)
+        self.L.nxref_ethash_hash(self.ctx(epoch), _in(header), nonce, f, m)
+        return bytes(f), bytes(m)
