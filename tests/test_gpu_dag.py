@@ -1,0 +1,111 @@
+"""K3 (DAG generation) / light cache / L1 cache parity on the GPU, through the C ABI.
+Bit-exact against the oracle, the reference-made fixtures and whole-DAG digests."""
+import ctypes as C
+import hashlib
+import random
+import struct
+
+import pytest
+from conftest import golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _dag_sha256(ctx, chunk_items=1 << 20):
+    h = hashlib.sha256()
+    m = ctx.dag_num_items
+    for first in range(0, m, chunk_items):
+        h.update(ctx.read_items(first, min(chunk_items, m - first)))
+    return h.hexdigest()
+
+
+def test_epoch0_context_fields_and_l1_kat(ctx_of, oracle):
+    ctx = ctx_of(0)
+    assert ctx.epoch_number == 0
+    assert (ctx.light_cache_num_items, ctx.full_dataset_num_items) == (262139, 8388593)
+    assert ctx.dag_num_items == 4194296
+    assert ctx.l1_cache[:20] == golden("kawpow_kats.json")["l1_epoch0_first20"]  # kawpow_tests.cpp:20-39
+    assert ctx.l1_cache == oracle.l1(0)
+    e = golden("epochs.json")
+    assert hashlib.sha256(ctx.light_cache).hexdigest() == e["light_cache_sha256_epoch0"]
+
+
+@pytest.mark.parametrize("epoch", [0, 448])
+def test_dag_items_vs_reference_fixture(ctx_of, epoch):
+    ctx = ctx_of(epoch)
+    g = golden("dag_items.json")[str(epoch)]
+    assert ctx.dag_num_items == g["num_items_256"]
+    for i, hx in g["items"].items():
+        assert ctx.read_items(int(i), 1).hex() == hx, i
+    for i, sha in g["shard_edges_sha256"].items():
+        assert hashlib.sha256(ctx.read_items(int(i), 1)).hexdigest() == sha, i
+    assert hashlib.sha256(ctx.read_items(0, 4096)).hexdigest() == g["first4096_sha256"]
+
+
+@pytest.mark.parametrize("epoch", [0, 448])
+def test_whole_dag_digest(ctx_of, epoch):
+    """Every byte of the DAG: sha256 and the position-weighted sum, vs the reference-computed digests."""
+    ctx = ctx_of(epoch)
+    g = golden("dag_digest.json")[str(epoch)]
+    assert ctx.dag_bytes == g["bytes"]
+    assert ctx.checksum() == g["weighted_sum"]
+    assert _dag_sha256(ctx) == g["sha256"]
+
+
+def test_dag_items_vs_oracle_live(ctx_of, oracle):
+    ctx = ctx_of(0)
+    rnd = random.Random(11)
+    m = ctx.dag_num_items
+    for i in [0, 1, m - 1] + [rnd.randrange(m) for _ in range(20)]:
+        assert ctx.read_items(i, 1) == oracle.dataset_item_2048(0, i)
+
+
+def test_generate_range_edges(nx, ctx_of):
+    """Ragged ranges (count not a multiple of the CTA's 32 items), first and last items, empty range."""
+    import torch
+    ctx = ctx_of(0)
+    m = ctx.dag_num_items
+    for first, count in [(0, 1), (5, 33), (m - 7, 7), (1000, 257), (m - 1, 1)]:
+        buf = torch.zeros(count * 256 + 256, dtype=torch.uint8, device="cuda:0")
+        ctx.generate_range(first, count, buf.data_ptr())
+        got = bytes(buf.cpu().numpy().tobytes())
+        assert got[:count * 256] == ctx.read_items(first, count)
+        assert got[count * 256:] == bytes(256)  # nothing written past the range
+    ctx.generate_range(10, 0, 0x1000)  # empty: no launch, no fault
+    with pytest.raises(nx.NxError):
+        ctx.generate_range(m - 1, 2, 0x1000)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_sharded_build_slices_equal_full_dag(nx, ctx_of, world):
+    """Each rank of an N-way build writes only its slice, at its final offset; the slices tile the DAG.
+    (Ranks emulated one after the other on cuda:0: no collective needed to check the slices.)"""
+    full = ctx_of(0)
+    m = full.dag_num_items
+    share = (m + world - 1) // world
+    for rank in sorted({0, 1, world - 1}):
+        c = nx.EpochContext(0, 0, rank=rank, world=world)
+        try:
+            assert c.dag_share_bytes == share * 256 and c.dag_padded_bytes == share * world * 256
+            first, last = rank * share, min(m, (rank + 1) * share)
+            for a in (first, (first + last) // 2, last - 1):
+                assert c.read_items(a, 1) == full.read_items(a, 1)
+            h1 = hashlib.sha256(c.read_items(first, min(4096, last - first))).hexdigest()
+            h2 = hashlib.sha256(full.read_items(first, min(4096, last - first))).hexdigest()
+            assert h1 == h2
+            with pytest.raises(nx.NxError):  # not finalized: hashing must refuse
+                nx.progpow.hash(c, 0, bytes(32), 0)
+        finally:
+            c.close()
+
+
+def test_light_cache_gpu_kernel_matches_host(nx, monkeypatch):
+    """K4 (serial chain on the device) produces the same light cache and DAG as the host build."""
+    monkeypatch.setenv("NX_LIGHT_CACHE", "gpu")
+    c = nx.EpochContext(0, 0)
+    try:
+        e = golden("epochs.json")
+        assert hashlib.sha256(c.light_cache).hexdigest() == e["light_cache_sha256_epoch0"]
+        assert hashlib.sha256(struct.pack("<4096I", *c.l1_cache)).hexdigest() == e["l1_sha256_epoch0"]
+    finally:
+        c.close()

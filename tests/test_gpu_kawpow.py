@@ -1,0 +1,170 @@
+"""KawPow parity on the GPU through the C ABI: every mix and final hash bit-exact against the
+reference's KATs, the reference-made fixtures (BASELINE config 1: 2^16 nonces) and the oracle live."""
+import hashlib
+import random
+
+import pytest
+from conftest import golden
+
+from nodexa_chain_core_b200 import progpow
+
+pytestmark = pytest.mark.gpu
+KATS = golden("kawpow_kats.json")
+
+
+def test_hash_and_verify_kats(ctx_of):
+    """kawpow_tests.cpp:75-107 (13 vectors, each with its two negative verify cases) + :58-73"""
+    for t in KATS["hash_cases"] + [KATS["hash_30000"]]:
+        ctx = ctx_of(t["height"] // 7500)
+        hd = bytes.fromhex(t["header"])
+        r = progpow.hash(ctx, t["height"], hd, t["nonce"])
+        assert r.mix_hash.hex() == t["mix"], t["height"]
+        assert r.final_hash.hex() == t["final"], t["height"]
+        assert progpow.verify(ctx, t["height"], hd, r.mix_hash, t["nonce"], r.final_hash)
+        lower = bytearray(r.final_hash)
+        lower[31] = (lower[31] - 1) & 0xff
+        assert not progpow.verify(ctx, t["height"], hd, r.mix_hash, t["nonce"], bytes(lower))
+        bad = bytearray(r.mix_hash)
+        bad[7] = (bad[7] + 1) & 0xff
+        assert not progpow.verify(ctx, t["height"], hd, bytes(bad), t["nonce"], r.final_hash)
+        assert progpow.hash_no_verify(t["height"], hd, r.mix_hash, t["nonce"]) == r.final_hash
+
+
+def test_hash_empty_descending_heights(ctx_of):
+    """kawpow_tests.cpp:41-56 hashes heights 1000..1 with the epoch-0 context and checks the last one.
+    (A subset of the heights: each distinct period costs one NVRTC compile.)"""
+    ctx = ctx_of(0)
+    r = None
+    for h in list(range(1000, 940, -7)) + list(range(12, 0, -1)):
+        r = progpow.hash(ctx, h, bytes(32), 0)
+    assert r.mix_hash.hex() == KATS["hash_cases"][0]["mix"]
+    assert r.final_hash.hex() == KATS["hash_cases"][0]["final"]
+
+
+def test_search_kat(ctx_of):
+    """kawpow_tests.cpp:109-140"""
+    ctx = ctx_of(0)
+    s = KATS["search"]
+    hd, b = bytes.fromhex(s["header"]), bytes.fromhex(s["boundary"])
+    sr = progpow.search(ctx, 0, hd, b, s["miss"]["start"], s["miss"]["iterations"])
+    assert (sr.solution_found, sr.nonce, sr.final_hash, sr.mix_hash) == (False, 0, bytes(32), bytes(32))
+    srl = progpow.search_light(ctx, 0, hd, b, s["miss"]["start"], s["miss"]["iterations"])
+    assert srl == sr
+    sr = progpow.search(ctx, 0, hd, b, s["hit"]["start"], s["hit"]["iterations"])
+    assert sr.solution_found and sr.nonce == s["hit"]["nonce"]
+    r = progpow.hash(ctx, 0, hd, 395)
+    assert (sr.final_hash, sr.mix_hash) == (r.final_hash, r.mix_hash)
+    assert sr.final_hash != bytes(32) and sr.mix_hash != bytes(32)
+
+
+def test_config1_all_65536_nonces(ctx_of):
+    """BASELINE.json configs[0]: 2^16 nonces over the fixed synthetic header at epoch 0, plus 2^12 nonces at
+    heights 1, 2, 3, 7499 — every {final, mix} against the fixture produced by the reference's progpow::hash."""
+    g = golden("kawpow_config1.json")
+    hh = bytes.fromhex(g["header_hash"])
+    ctx = ctx_of(0)
+    for run in g["runs"]:
+        buf = progpow.hash_batch(ctx, run["height"], hh, run["start"], run["count"])
+        assert len(buf) == run["count"] * 64
+        assert buf[:16 * 64].hex() == run["first16"]
+        per = [hashlib.sha256(buf[i:i + 256 * 64]).hexdigest() for i in range(0, len(buf), 256 * 64)]
+        bad = [i for i, (a, b) in enumerate(zip(per, run["sha256_per_256_nonces"])) if a != b]
+        assert not bad, f"height {run['height']}: mismatching 256-nonce chunks {bad[:8]}"
+        assert hashlib.sha256(buf).hexdigest() == run["sha256_all"]
+    z = progpow.hash_batch(ctx, 0, bytes(32), 0, 1024)
+    assert hashlib.sha256(z).hexdigest() == g["zero_header_first1024_sha256"]
+
+
+def test_epoch448_vs_reference_fixture(ctx_of):
+    """BASELINE.json configs[1]'s epoch (4.5 GiB DAG): 8 headers x 16 nonces made by the reference's code."""
+    k = golden("kawpow_epoch448.json")
+    ctx = ctx_of(448)
+    for c in k["cases"]:
+        buf = progpow.hash_batch(ctx, c["height"], bytes.fromhex(c["header"]), c["start"], c["count"])
+        assert buf.hex() == c["out"], c["height"]
+
+
+def test_random_inputs_vs_oracle_live(ctx_of, oracle):
+    rnd = random.Random(20261106)
+    ctx = ctx_of(0)
+    for _ in range(6):
+        hd = rnd.randbytes(32)
+        height = rnd.randrange(0, 7500)
+        start = rnd.getrandbits(64) - 40
+        got = progpow.hash_batch(ctx, height, hd, start & (2**64 - 1), 24)
+        want = oracle.kawpow_hash_range(0, height, hd, start & (2**64 - 1), 24)
+        assert got == want
+
+
+def test_ragged_and_empty_batches(ctx_of, oracle):
+    ctx = ctx_of(0)
+    hd = bytes(range(32))
+    ref_1k = progpow.hash_batch(ctx, 5, hd, 1000, 1024)
+    assert progpow.hash_batch(ctx, 5, hd, 1000, 0) == b""
+    for count in (1, 15, 16, 17, 255, 256, 257, 1000):
+        assert progpow.hash_batch(ctx, 5, hd, 1000, count) == ref_1k[:count * 64]
+    # a window that does not start on a 16-nonce boundary relative to the first batch
+    assert progpow.hash_batch(ctx, 5, hd, 1007, 300) == ref_1k[7 * 64:307 * 64]
+    assert ref_1k[:8 * 64] == oracle.kawpow_hash_range(0, 5, hd, 1000, 8)
+    # nonce arithmetic wraps modulo 2^64 like the reference's uint64_t
+    top = progpow.hash_batch(ctx, 5, hd, 2**64 - 4, 4)
+    assert top == oracle.kawpow_hash_range(0, 5, hd, 2**64 - 4, 4)
+
+
+def test_hash_batch_device_equals_host(ctx_of):
+    import torch
+    ctx = ctx_of(0)
+    hd = hashlib.sha256(b"dev").digest()
+    n = 5000
+    out = torch.zeros(n * 64 + 64, dtype=torch.uint8, device="cuda:0")
+    progpow.hash_batch_device(ctx, 77, hd, 123456789, n, out.data_ptr())
+    got = out.cpu().numpy().tobytes()
+    assert got[:n * 64] == progpow.hash_batch(ctx, 77, hd, 123456789, n)
+    assert got[n * 64:] == bytes(64)
+
+
+def test_search_returns_lowest_nonce_across_batches(ctx_of):
+    """progpow.cpp:572-577: the FIRST hit of an ascending scan, not the first to be found.  Checked against
+    a host-side scan of the batch-hash output, over a range spanning several internal launches."""
+    ctx = ctx_of(0)
+    hd = hashlib.sha256(b"search").digest()
+    n = (1 << 22) + 12345  # more than one internal batch, ragged tail
+    start = 0x1234567800000000
+    allh = progpow.hash_batch(ctx, 300, hd, start, n)
+    finals = [allh[i * 64:i * 64 + 32] for i in range(n)]
+    for bits in (12, 20):  # about n/2^bits hits
+        boundary = ((1 << (256 - bits)) - 1).to_bytes(32, "big")
+        hits = [i for i, f in enumerate(finals) if f <= boundary]
+        sr = progpow.search(ctx, 300, hd, boundary, start, n)
+        if hits:
+            assert sr.solution_found and sr.nonce == start + hits[0]
+            assert sr.final_hash == finals[hits[0]] and sr.mix_hash == allh[hits[0] * 64 + 32:hits[0] * 64 + 64]
+            # a window that ends just before the first hit finds nothing; one that starts after finds the next
+            sr0 = progpow.search(ctx, 300, hd, boundary, start, hits[0])
+            assert not sr0.solution_found and sr0.nonce == 0
+            if len(hits) > 1:
+                sr1 = progpow.search(ctx, 300, hd, boundary, start + hits[0] + 1, n - hits[0] - 1)
+                assert sr1.solution_found and sr1.nonce == start + hits[1]
+        else:
+            assert not sr.solution_found
+    # exact-boundary case: final == boundary qualifies (is_less_or_equal)
+    sr = progpow.search(ctx, 300, hd, finals[100], start + 100, 1)
+    assert sr.solution_found and sr.nonce == start + 100
+    below = (int.from_bytes(finals[100], "big") - 1).to_bytes(32, "big")
+    assert not progpow.search(ctx, 300, hd, below, start + 100, 1).solution_found
+    assert not progpow.search(ctx, 300, hd, boundary, start, 0).solution_found
+
+
+def test_search_enqueue_sync_pipelining(ctx_of):
+    """Several enqueued batches, one sync: the lowest hit over all of them."""
+    ctx = ctx_of(0)
+    hd = hashlib.sha256(b"pipe").digest()
+    boundary = ((1 << (256 - 14)) - 1).to_bytes(32, "big")
+    ref = progpow.search(ctx, 9, hd, boundary, 5000, 3 * 65536)
+    for k in range(3):
+        progpow.search_enqueue(ctx, 9, hd, boundary, 5000 + k * 65536, 65536)
+    sr = progpow.search_sync(ctx)
+    assert sr == ref
+    ms, launches = ctx.last_timing()
+    assert launches >= 3 and ms > 0
+    assert progpow.search_sync(ctx) == progpow.SearchResult()  # nothing pending

@@ -1,0 +1,97 @@
+"""Host-side product code (csrc/nx_host.cpp) against the golden fixtures and the oracle: epoch geometry,
+Keccak, hash_no_verify, header hash, compact target.  No GPU needed."""
+import ctypes as C
+import random
+import struct
+
+from conftest import golden
+
+from nodexa_chain_core_b200 import ethash, progpow
+from nodexa_chain_core_b200._lib import inb, lib, outb
+
+
+def test_epoch_geometry_vs_golden():
+    e = golden("epochs.json")
+    for k, (light, full) in e["sizes"].items():
+        assert ethash.calculate_light_cache_num_items(int(k)) == light
+        assert ethash.calculate_full_dataset_num_items(int(k)) == full
+    for k, s in e["seeds"].items():
+        assert ethash.calculate_epoch_seed(int(k)).hex() == s
+    for s, n in e["find_epoch"].items():
+        assert ethash.find_epoch_number(bytes.fromhex(s)) == n  # includes the not-found (-1) case
+    assert ethash.get_epoch_number(0) == 0 and ethash.get_epoch_number(7499) == 0
+    assert ethash.get_epoch_number(7500) == 1 and ethash.get_epoch_number(3360000) == 448
+
+
+def test_primes_edge_cases(oracle):
+    for ub in (-5, 0, 1, 2, 3, 4, 9, 10, 97, 100, 262144, 8388608):
+        assert lib.nx_find_largest_prime(ub) == oracle.L.nxo_find_largest_prime(ub)
+    assert lib.nx_find_largest_prime(1) == 0 and lib.nx_find_largest_prime(2) == 2
+
+
+def test_keccak_vs_golden_and_oracle(oracle):
+    m = golden("misc.json")
+    d = bytes(range(256)) * 2
+    for ln, (h256, h512) in m["keccak"].items():
+        assert ethash.keccak256(d[:int(ln)]).hex() == h256
+        assert ethash.keccak512(d[:int(ln)]).hex() == h512
+    st = (C.c_uint32 * 25)(*range(1, 26))
+    lib.nx_keccakf800(st)
+    assert list(st) == m["keccakf800_of_1to25"]
+    st64 = (C.c_uint64 * 25)(*range(1, 26))
+    lib.nx_keccakf1600(st64)
+    assert [str(x) for x in st64] == m["keccakf1600_of_1to25"]
+    rnd = random.Random(1)
+    for ln in (0, 5, 71, 72, 135, 136, 137, 1000):
+        b = rnd.randbytes(ln)
+        assert ethash.keccak256(b) == oracle.keccak256(b)
+        assert ethash.keccak512(b) == oracle.keccak512(b)
+
+
+def test_hash_no_verify_vs_golden_and_kats():
+    for c in golden("misc.json")["hash_no_verify"]:
+        assert progpow.hash_no_verify(0, bytes.fromhex(c["header"]), bytes.fromhex(c["mix"]),
+                                      c["nonce"]).hex() == c["final"]
+    # the final hash of every reference KAT is reproduced from its mix without the DAG
+    for t in golden("kawpow_kats.json")["hash_cases"]:
+        assert progpow.hash_no_verify(t["height"], bytes.fromhex(t["header"]), bytes.fromhex(t["mix"]),
+                                      t["nonce"]).hex() == t["final"]
+
+
+def test_header_hash_and_sha256d(oracle):
+    g = golden("kawpow_config1.json")
+    raw = bytes.fromhex(g["header_input_80B"])
+    v, prev, merkle, t, bits, h = struct.unpack("<i32s32sIII", raw)
+    o = outb(32)
+    lib.nx_kawpow_header_hash(v, inb(prev), inb(merkle), t, bits, h, o)
+    assert bytes(o).hex() == g["header_hash"]
+    import hashlib
+    rnd = random.Random(2)
+    for ln in (0, 1, 55, 56, 63, 64, 80, 119, 120, 200):
+        b = rnd.randbytes(ln)
+        lib.nx_sha256d(inb(b) if b else outb(1), ln, o)
+        assert bytes(o) == hashlib.sha256(hashlib.sha256(b).digest()).digest()
+
+
+def test_compact_to_boundary_vs_oracle(oracle):
+    rnd = random.Random(3)
+    cases = [0, 0x207fffff, 0x2000ffff, 0x1e00ffff, 0x1d00ffff, 0x01003456, 0x01803456, 0x02008000, 0x03123456,
+             0x04923456, 0x20123456, 0x21123456, 0x22123456, 0x23000001, 0xff123456, 0x1b0404cb]
+    cases += [rnd.getrandbits(32) for _ in range(2000)]
+    for bits in cases:
+        o = outb(32)
+        ok = lib.nx_compact_to_boundary(bits, o)
+        ook, ob = oracle.compact_to_boundary(bits)
+        assert (bool(ok), bytes(o)) == (ook, ob), hex(bits)
+
+
+def test_check_proof_of_work():
+    limit = bytes.fromhex("00" + "ff" * 31)  # kawpowLimit, chainparams.cpp:116-117
+    o = outb(32)
+    assert lib.nx_compact_to_boundary(0x1e00ffff, o)
+    target = bytes(o)
+    assert lib.nx_check_proof_of_work(inb(target), 0x1e00ffff, inb(limit)) == 1
+    above = (int.from_bytes(target, "big") + 1).to_bytes(32, "big")
+    assert lib.nx_check_proof_of_work(inb(above), 0x1e00ffff, inb(limit)) == 0
+    assert lib.nx_check_proof_of_work(inb(bytes(32)), 0x207fffff, inb(limit)) == 0  # target above powLimit
+    assert lib.nx_check_proof_of_work(inb(bytes(32)), 0, inb(limit)) == 0           # zero target
