@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""bench.py — KawPow nonce-search throughput (MH/s) on B200, against the HBM roofline.
+
+Workload (BASELINE.json configs[1]): KawPow search at the mainnet-sized epoch 448 (4.50 GiB DAG), synthetic
+header hashes keccak256(u64 seed), start nonce = seed << 32, boundary 0 (never hits: pure throughput).
+A "step" is one pass of the search kernel over one batch of --batch nonces (default 2^24 = 256 GiB of
+algorithmic DAG reads), with a fresh header every step.  The DAG (4.5 GiB) and each step's 256 GiB of random
+reads are far larger than the 126 MB L2, so no L2 flush is needed between steps.
+
+  python bench.py --gpus 1 --steps 20 --warmup 3
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+         bench.py --gpus N --steps K --warmup W        (one rank per GPU; nonce super-batches are sharded)
+  python bench.py --impl reference ...                 (the reference's CPU progpow::hash on the host cores)
+
+Prints ONE JSON line (rank 0).  Only the `cpu_baseline` leg and `--impl reference` touch oracle/.
+"""
+import argparse
+import json
+import os
+import struct
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+DAG_BYTES_PER_HASH = 64 * 256  # 64 rounds x one 256-byte item (reference progpow.cpp:275-276,182-186)
+EPOCH = 448
+HEIGHT = EPOCH * 7500
+
+
+def header_for(seed: int, keccak256) -> bytes:
+    return keccak256(struct.pack("<Q", seed))
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [x.strip() for x in out.strip().split(",")]
+                if len(parts) >= 7:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
+        pw = [float(r[2]) for r in self.rows if r[2].replace(".", "", 1).isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "power_w_max": max(pw) if pw else None, "samples": len(self.rows)}
+
+
+def cpu_reference_rate(sample_nonces: int, threads: int):
+    """The reference's own CPU path (light context, progpow::hash — what the node runs, src/hash.cpp:258-277)
+    on the host cores: oracle/_ref when it was built, else the oracle port."""
+    from oracle.oracle import Oracle, Ref
+    impl = Ref() if Ref.available() else Oracle()
+    t0 = time.perf_counter()
+    impl.ctx(EPOCH)  # light cache build (serial), reported separately
+    ctx_s = time.perf_counter() - t0
+    hd = impl.keccak256(struct.pack("<Q", 1))
+    impl.kawpow_hash_range(EPOCH, HEIGHT, hd, 1 << 32, min(threads, sample_nonces), threads)  # warm
+    t0 = time.perf_counter()
+    impl.kawpow_hash_range(EPOCH, HEIGHT, hd, 1 << 32, sample_nonces, threads)
+    dt = time.perf_counter() - t0
+    return impl.kind, sample_nonces / dt / 1e6, dt, ctx_s
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step = max(cores * 8, 64)
+    from oracle.oracle import Oracle, Ref
+    impl = Ref() if Ref.available() else Oracle()
+    impl.ctx(EPOCH)
+    times = []
+    for k in range(args.warmup + args.steps):
+        hd = impl.keccak256(struct.pack("<Q", k + 1))
+        t0 = time.perf_counter()
+        impl.kawpow_hash_range(EPOCH, HEIGHT + k, hd, (k + 1) << 32, per_step, cores)
+        if k >= args.warmup:
+            times.append(time.perf_counter() - t0)
+    total = sum(times)
+    mhs = per_step * args.steps / total / 1e6
+    sample = f"{per_step} nonces/step x {args.steps} steps, light context (progpow::hash as src/hash.cpp:273 calls it)"
+    line = {"impl": "reference", "metric": "KawPow MH/s", "value": mhs, "unit": "MH/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": "kawpow_search_epoch448", "epoch": EPOCH, "dag_bytes": 4831835648,
+                       "nonces_per_step": per_step},
+            "cpu_baseline": {"value": mhs, "unit": "MH/s", "cores": cores, "kind": impl.kind, "sample": sample},
+            "e2e": {"value": mhs, "unit": "MH/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=1 << 24, help="nonces per step per GPU")
+    ap.add_argument("--epoch", type=int, default=EPOCH)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+
+    import nodexa_chain_core_b200 as nx
+    from nodexa_chain_core_b200 import ethash, progpow
+
+    if nx.lib.nx_device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+
+    epoch, height = args.epoch, args.epoch * 7500
+    # ---- epoch context: light cache + DAG.  N>1: each rank builds 1/N of the DAG, one in-place all-gather ----
+    t0 = time.perf_counter()
+    ctx = nx.EpochContext(epoch, local, rank=rank, world=world)
+    light_ms, dag_ms = ctx.build_times_ms()
+    allgather_ms = 0.0
+    if world > 1:
+        dag = ctx.dag_tensor()
+        share = ctx.dag_share_bytes
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0.record()
+        dist.all_gather_into_tensor(dag, dag[rank * share:(rank + 1) * share])
+        e1.record()
+        torch.cuda.synchronize()
+        allgather_ms = e0.elapsed_time(e1)
+        ctx.finalize()
+    build_s = time.perf_counter() - t0
+    checksum = ctx.checksum()
+
+    boundary = bytes(32)  # nothing qualifies: the kernel scans every nonce of the batch
+    B = args.batch
+    progpow.prepare(ctx, height)  # NVRTC-compile the period program off the clock
+
+    def step_enqueue(k):
+        # rank g of N scans super-batch k*N+g of header 1's nonce space
+        hd = header_for(1, ethash.keccak256)
+        start = ((1 << 32) + (k * world + rank) * B) & (2**64 - 1)
+        progpow.search_enqueue(ctx, height, hd, boundary, start, B)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident throughput: K kernels back to back, CUDA events on the launching stream ----
+    for k in range(args.warmup):
+        step_enqueue(k)
+    progpow.search_sync(ctx)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    w0 = time.perf_counter()
+    for k in range(args.steps):
+        step_enqueue(args.warmup + k)
+    sr = progpow.search_sync(ctx)
+    barrier()
+    wall_s = time.perf_counter() - w0
+    clocks = sampler.summary()
+    kernel_ms, launches = ctx.last_timing()
+    assert not sr.solution_found and launches == args.steps
+
+    # ---- end to end through the C ABI with HOST buffers: header+boundary in, search_result out, per step ----
+    e2e_steps = max(3, min(args.steps, 10))
+    progpow.search(ctx, height, header_for(999, ethash.keccak256), boundary, 0, 1 << 20)
+    barrier()
+    e0 = time.perf_counter()
+    for k in range(e2e_steps):
+        hd = header_for(1000 + k, ethash.keccak256)
+        start = (((1000 + k) << 32) + rank * B) & (2**64 - 1)
+        r = progpow.search(ctx, height, hd, boundary, start, B)
+        assert not r.solution_found
+    barrier()
+    e2e_s = time.perf_counter() - e0
+
+    # ---- max over ranks ----
+    t = torch.tensor([kernel_ms, e2e_s * 1e3, wall_s * 1e3, dag_ms, light_ms, allgather_ms], dtype=torch.float64,
+                     device=f"cuda:{local}")
+    cs = torch.tensor([checksum & 0x7fffffffffffffff], dtype=torch.int64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        cmin, cmax = cs.clone(), cs.clone()
+        dist.all_reduce(cmin, op=dist.ReduceOp.MIN)
+        dist.all_reduce(cmax, op=dist.ReduceOp.MAX)
+        assert cmin.item() == cmax.item(), "DAG checksum differs between ranks after the all-gather"
+    kernel_ms, e2e_ms, wall_ms, dag_ms, light_ms, allgather_ms = t.tolist()
+
+    if rank == 0:
+        total_hashes = B * args.steps * world
+        mhs = total_hashes / (kernel_ms * 1e-3) / 1e6
+        e2e_mhs = B * e2e_steps * world / (e2e_ms * 1e-3) / 1e6
+        peak, peak_src = measured_peak_gbs()
+        per_launch_ms = kernel_ms / args.steps
+        achieved = B * DAG_BYTES_PER_HASH / (per_launch_ms * 1e-3) / 1e9  # per GPU, per launch
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "kawpow_traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+            except Exception:
+                pass
+        line = {
+            "metric": "KawPow MH/s", "value": mhs, "unit": "MH/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": per_launch_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": "kawpow_search_epoch448" if epoch == EPOCH else f"kawpow_search_epoch{epoch}",
+                       "epoch": epoch, "height": height, "dag_bytes": ctx.dag_bytes, "nonces_per_step_per_gpu": B,
+                       "boundary": "0 (no hit)", "l2": "inputs larger than L2 (4.5 GiB DAG, random 256 B reads)",
+                       "sharding": f"nonce super-batches round-robin over {world} GPU(s); DAG built 1/{world} per GPU"
+                                   + (" + one NCCL all-gather" if world > 1 else ""),
+                       "dag_checksum": checksum},
+            "wall_ms_per_step": wall_ms / args.steps,
+            "e2e": {"value": e2e_mhs, "unit": "MH/s", "h2d_bytes_per_step": 64 + 24 + 8, "d2h_bytes_per_step": 8,
+                    "steps": e2e_steps, "api": "nx_kawpow_search (C ABI, host header/boundary in, search_result out)"},
+            "gpu_launches": args.steps + e2e_steps * ((B + (1 << 22) - 1) // (1 << 22)),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_hash": DAG_BYTES_PER_HASH, "kernel": "nx_kawpow_search_kernel",
+                         "roofline_mhs": peak * 1e9 / DAG_BYTES_PER_HASH / 1e6},
+            "clocks": clocks,
+            "epoch_build": {"light_cache_ms": light_ms, "dag_kernel_ms": dag_ms, "allgather_ms": allgather_ms,
+                            "total_s": build_s, "dag_gbs_written": ctx.dag_bytes / world / (dag_ms * 1e-3) / 1e9},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            sample = max(cores * 16, 128)
+            kind, cpu_mhs, dt, ctx_s = cpu_reference_rate(sample, cores)
+            line["cpu_baseline"] = {"value": cpu_mhs, "unit": "MH/s", "cores": cores, "kind": kind,
+                                    "sample": f"{sample} nonces of the same workload, light context "
+                                              f"(progpow::hash), {dt:.1f} s; context build {ctx_s:.1f} s excluded"}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -145,7 +145,8 @@ int nx_kawpow_search(const nx_epoch* ctx, int block_number, const uint8_t header
 
 /* Throughput form of the search for benchmarking/pipelining: enqueue the scan of one batch on the
  * context's stream without synchronising.  nx_kawpow_search_sync() waits and reports the lowest hit
- * of everything enqueued since the last sync. */
+ * of everything enqueued since the last sync.  Batches enqueued between two syncs must share
+ * header_hash and block_number and must not start below the first batch (NX_ERR_STATE otherwise). */
 int nx_kawpow_search_enqueue(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32],
                              const uint8_t boundary[32], uint64_t start_nonce, uint64_t count);
 int nx_kawpow_search_sync(const nx_epoch* ctx, nx_search_result* out);

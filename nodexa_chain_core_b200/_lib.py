@@ -92,6 +92,7 @@ def _load() -> C.CDLL:
         "nx_kawpow_program_source": (sz, [u64, u32, i, C.c_char_p, sz]),
         "nx_kawpow_program_ops": (i, [u64, C.POINTER(u32 * 6), i]),
         "nx_kawpow_compile_cubin": (C.c_long, [u64, u32, C.c_char_p, sz]),
+        "nx_host_light_cache": (None, [i, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

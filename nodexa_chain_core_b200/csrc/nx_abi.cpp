@@ -409,6 +409,10 @@ int nx_kawpow_search_enqueue(const nx_epoch* cc, int block_number, const uint8_t
         c->pending_block = block_number;
         std::memcpy(c->pending_header, header_hash, 32);
         c->launches_since_sync = 0;
+    } else if (block_number != c->pending_block || std::memcmp(header_hash, c->pending_header, 32) != 0 ||
+               start_nonce < c->pending_base) {
+        set_error("batches enqueued between two syncs must share header and block number and ascend in nonce");
+        return NX_ERR_STATE;
     }
     KawpowJob job;
     fill_job(job, header_hash, boundary, start_nonce, count, start_nonce - c->pending_base);

@@ -52,3 +52,13 @@ long nx_kawpow_compile_cubin(uint64_t prog_seed, uint32_t dag_items_256, char* b
 }
 
 }  // extern "C"
+
+extern "C" {
+// The product's host light-cache builder on its own (CPU tests compare it with the reference-made digest).
+void nx_host_light_cache(int epoch, uint8_t* out)
+{
+    uint8_t seed[32];
+    nx_epoch_seed(epoch, seed);
+    host_build_light_cache(out, nx_light_cache_num_items(epoch), seed);
+}
+}

@@ -95,3 +95,20 @@ def test_check_proof_of_work():
     assert lib.nx_check_proof_of_work(inb(above), 0x1e00ffff, inb(limit)) == 0
     assert lib.nx_check_proof_of_work(inb(bytes(32)), 0x207fffff, inb(limit)) == 0  # target above powLimit
     assert lib.nx_check_proof_of_work(inb(bytes(32)), 0, inb(limit)) == 0           # zero target
+
+
+def test_host_light_cache_vs_reference_digest():
+    """The product's own (host) light-cache chain for epoch 0 and the mainnet-sized epoch 448."""
+    import hashlib
+    import time
+    e = golden("epochs.json")
+    for epoch in (0, 448):
+        n = ethash.calculate_light_cache_num_items(epoch)
+        buf = C.create_string_buffer(n * 64)
+        t = time.time()
+        lib.nx_host_light_cache(epoch, buf)
+        dt = time.time() - t
+        assert hashlib.sha256(buf.raw).hexdigest() == e[f"light_cache_sha256_epoch{epoch}"]
+        assert buf.raw[:64].hex() == e[f"light_cache_first64_epoch{epoch}"]
+        assert buf.raw[-64:].hex() == e[f"light_cache_last64_epoch{epoch}"]
+        print(f"epoch {epoch}: host light cache {dt:.2f} s")
