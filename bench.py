@@ -79,27 +79,32 @@ class ClockSampler(threading.Thread):
                 "power_w_max": max(pw) if pw else None, "samples": len(self.rows)}
 
 
-def cpu_reference_rate(sample_nonces: int, threads: int):
+def cpu_reference_rate(target_s: float, threads: int):
     """The reference's own CPU path (light context, progpow::hash — what the node runs, src/hash.cpp:258-277)
-    on the host cores: oracle/_ref when it was built, else the oracle port."""
+    on the host cores: oracle/_ref when it was built, else the oracle port.  A short probe sizes the timed
+    sample so that it takes about target_s seconds of wall time on `threads` threads."""
     from oracle.oracle import Oracle, Ref
     impl = Ref() if Ref.available() else Oracle()
     t0 = time.perf_counter()
     impl.ctx(EPOCH)  # light cache build (serial), reported separately
     ctx_s = time.perf_counter() - t0
     hd = impl.keccak256(struct.pack("<Q", 1))
-    impl.kawpow_hash_range(EPOCH, HEIGHT, hd, 1 << 32, min(threads, sample_nonces), threads)  # warm
+    probe = threads * 4
     t0 = time.perf_counter()
-    impl.kawpow_hash_range(EPOCH, HEIGHT, hd, 1 << 32, sample_nonces, threads)
+    impl.kawpow_hash_range(EPOCH, HEIGHT, hd, 1 << 32, probe, threads)  # also warms the light cache
+    rate = probe / (time.perf_counter() - t0)
+    sample = max(probe, int(rate * target_s) // threads * threads)
+    t0 = time.perf_counter()
+    impl.kawpow_hash_range(EPOCH, HEIGHT, hd, (1 << 32) + probe, sample, threads)
     dt = time.perf_counter() - t0
-    return impl.kind, sample_nonces / dt / 1e6, dt, ctx_s
+    return impl.kind, sample, sample / dt / 1e6, dt, ctx_s
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    per_step = max(cores * 8, 64)
+    per_step = max(cores * 64, 256)  # ~0.25 s of CPU work per step on this class of host
     from oracle.oracle import Oracle, Ref
     impl = Ref() if Ref.available() else Oracle()
     impl.ctx(EPOCH)
@@ -127,7 +132,7 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=1 << 24, help="nonces per step per GPU")
     ap.add_argument("--epoch", type=int, default=EPOCH)
@@ -274,8 +279,7 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            sample = max(cores * 16, 128)
-            kind, cpu_mhs, dt, ctx_s = cpu_reference_rate(sample, cores)
+            kind, sample, cpu_mhs, dt, ctx_s = cpu_reference_rate(15.0, cores)
             line["cpu_baseline"] = {"value": cpu_mhs, "unit": "MH/s", "cores": cores, "kind": kind,
                                     "sample": f"{sample} nonces of the same workload, light context "
                                               f"(progpow::hash), {dt:.1f} s; context build {ctx_s:.1f} s excluded"}
