@@ -102,6 +102,30 @@ int nx_dag_read_items(const nx_epoch* ctx, uint32_t first, uint32_t count, uint8
  * No reference counterpart (test/ops aid: equal on every GPU after the all-gather). */
 int nx_dag_checksum(const nx_epoch* ctx, uint64_t* out);
 
+/* The same weighted sum for callers that must not allocate.  No counterpart in the reference.
+ *
+ * Who needs it: code that runs next to a live search - cudaMalloc/cudaFree stall every stream of the
+ * device while they run, so a DAG integrity check from a watchdog or validation thread would punch a
+ * hole into the hash rate - and plug-ins living inside a host application that owns the whole HBM
+ * budget and hands out pointers but forbids allocations.  nx_dag_checksum above uses a buffer the
+ * epoch context cudaMalloc'ed; this variant keeps its per-block partial sums in a fixed 16.25 KiB array
+ * that is part of the library image (each GPU that loads the library holds it until the process exits),
+ * and calls no cudaMalloc, cudaFree or any allocating library routine.
+ *
+ *   data_device  device memory of the CURRENT device, 8-byte aligned (e.g. nx_epoch_dag_ptr())
+ *   n_bytes      multiple of 8, at most NX_NOALLOC_MAX_BYTES (larger inputs are refused with
+ *                NX_ERR_INVALID and a message; use nx_dag_checksum for those)
+ *   stream       cudaStream_t to run on (NULL = default stream); the call returns after it completed
+ *   out_host     receives the sum (same value as nx_dag_checksum over the same bytes)
+ *
+ * The first call on each device looks up the device address of the array (one-time set-up), so make
+ * that first call before starting any stream capture on that device.  All calls share the one
+ * array and it keeps whatever the previous call left in it; nothing in it needs to be zero at entry
+ * (every slot is rewritten before it is read), but two calls that overlap on the same GPU - from two
+ * threads or two streams - race on it: serialise them. */
+#define NX_NOALLOC_MAX_BYTES (8ull << 30)
+int nx_dag_checksum_noalloc(const void* data_device, size_t n_bytes, void* stream, uint64_t* out_host);
+
 /* ------------------------------------------------------------------------------------------------
  * KawPow. */
 typedef struct nx_result

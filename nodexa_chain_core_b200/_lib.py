@@ -73,6 +73,7 @@ def _load() -> C.CDLL:
         "nx_dag_generate_range": (i, [vp, u32, u32, vp]),
         "nx_dag_read_items": (i, [vp, u32, u32, u8p]),
         "nx_dag_checksum": (i, [vp, C.POINTER(u64)]),
+        "nx_dag_checksum_noalloc": (i, [vp, sz, vp, C.POINTER(u64)]),
         "nx_kawpow_prepare": (i, [vp, i]),
         "nx_kawpow_hash": (i, [vp, i, u8p, u64, C.POINTER(NxResult)]),
         "nx_kawpow_hash_batch": (i, [vp, i, u8p, u64, u64, vp]),

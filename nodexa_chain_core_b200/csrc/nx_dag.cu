@@ -16,6 +16,8 @@
 #include "nx_internal.hpp"
 #include "nx_keccak.cuh"
 
+#include <mutex>
+
 namespace nx
 {
 namespace
@@ -199,8 +201,111 @@ __global__ void light_cache_kernel(uint64_t* __restrict__ cache, uint32_t n, uin
         }
     }
 }
+// ---- allocation-free DAG checksum (see nx_dag_checksum_noalloc in include/nx_kawpow.h) ----
+// Same weighted sum as checksum_partial_kernel, but the per-CTA partial sums live in a fixed array
+// inside the library image instead of a buffer the context cudaMalloc'ed.  One CTA reduces one
+// contiguous 4 MiB chunk, so the number of partials - and with it the largest input the fixed array
+// can serve - is known up front.  Every GPU that loads the library keeps these 16.25 KiB until exit.
+constexpr size_t NOALLOC_CHUNK_WORDS = (size_t)1 << 19;  // 2^19 u64 words = 4 MiB per CTA
+constexpr int NOALLOC_MAX_PARTIALS = 2048;                // x 4 MiB = 8 GiB of input at most
+constexpr int NOALLOC_RESULT_SLOT = NOALLOC_MAX_PARTIALS; // one more u64, 256-byte aligned, for the total
+static __device__ __align__(256) uint64_t g_noalloc_scratch[NOALLOC_MAX_PARTIALS + 32];
+
+__global__ void __launch_bounds__(CSUM_THREADS)
+checksum_chunk_kernel(const uint64_t* __restrict__ words, size_t n, uint64_t* __restrict__ partials)
+{
+    __shared__ uint64_t red[CSUM_THREADS / 32];
+    const size_t begin = (size_t)blockIdx.x * NOALLOC_CHUNK_WORDS;
+    const size_t end = begin + NOALLOC_CHUNK_WORDS < n ? begin + NOALLOC_CHUNK_WORDS : n;
+    uint64_t acc = 0;
+    for (size_t i = begin + threadIdx.x; i < end; i += CSUM_THREADS) acc += __ldg(words + i) * (2 * (uint64_t)i + 1);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t s = 0;
+        for (int i = 0; i < CSUM_THREADS / 32; ++i) s += red[i];
+        partials[blockIdx.x] = s;  // written unconditionally: no slot that is read later keeps an old value
+    }
+}
+
+// Host code may not use g_noalloc_scratch as a pointer: on the host that name is only a handle for the
+// device symbol.  The real device address is looked up once per device and kept here.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+uint64_t* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
 }  // namespace
 
+}  // namespace nx
+
+extern "C" int nx_dag_checksum_noalloc(const void* data_device, size_t n_bytes, void* stream, uint64_t* out_host)
+{
+    using namespace nx;
+    if (!data_device || !out_host) {
+        set_error("nx_dag_checksum_noalloc: null argument");
+        return NX_ERR_INVALID;
+    }
+    if (n_bytes % 8 != 0 || ((uintptr_t)data_device & 7) != 0) {
+        set_error("nx_dag_checksum_noalloc: data must be 8-byte aligned and a whole number of 64-bit words");
+        return NX_ERR_INVALID;
+    }
+    const size_t n_words = n_bytes / 8;
+    const size_t chunks = (n_words + NOALLOC_CHUNK_WORDS - 1) / NOALLOC_CHUNK_WORDS;
+    if (chunks > (size_t)NOALLOC_MAX_PARTIALS) {
+        set_error("nx_dag_checksum_noalloc: %zu bytes exceed the fixed scratch (limit %llu bytes = %d chunks of 4 MiB); "
+                  "use nx_dag_checksum for larger inputs",
+                  n_bytes, (unsigned long long)NX_NOALLOC_MAX_BYTES, NOALLOC_MAX_PARTIALS);
+        return NX_ERR_INVALID;
+    }
+    int dev = -1;
+    NX_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+        set_error("nx_dag_checksum_noalloc: device index %d not supported", dev);
+        return NX_ERR_INVALID;
+    }
+    cudaPointerAttributes attr;
+    NX_CUDA(cudaPointerGetAttributes(&attr, data_device));
+    if (attr.type != cudaMemoryTypeDevice || attr.device != dev) {
+        set_error("nx_dag_checksum_noalloc: data is not device memory of the current device %d "
+                  "(make the device that owns it current first)", dev);
+        return NX_ERR_INVALID;
+    }
+    uint64_t* scratch = nullptr;
+    {
+        // One-time set-up per device, with that device current: resolve the symbol to its device address.
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[dev]) {
+            void* p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) {
+                set_error("cudaGetSymbolAddress(g_noalloc_scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+                cudaGetLastError();
+                return NX_ERR_CUDA;
+            }
+            g_noalloc_ptr[dev] = static_cast<uint64_t*>(p);
+        }
+        scratch = g_noalloc_ptr[dev];
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (chunks == 0) {
+        *out_host = 0;
+        return NX_OK;
+    }
+    // Nothing in the array has to start at zero: partial[0..chunks) and the result slot are all
+    // overwritten by this call before they are read, whatever the previous call left behind.
+    checksum_chunk_kernel<<<(unsigned)chunks, CSUM_THREADS, 0, s>>>(static_cast<const uint64_t*>(data_device), n_words,
+                                                                   scratch);
+    NX_CUDA(cudaGetLastError());
+    checksum_final_kernel<<<1, 32, 0, s>>>(scratch, (int)chunks, scratch + NOALLOC_RESULT_SLOT);
+    NX_CUDA(cudaGetLastError());
+    NX_CUDA(cudaMemcpyAsync(out_host, scratch + NOALLOC_RESULT_SLOT, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+    NX_CUDA(cudaStreamSynchronize(s));
+    return NX_OK;
+}
+
+namespace nx
+{
 int dag_generate(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256, void* out_dev,
                  cudaStream_t s)
 {
