@@ -109,3 +109,18 @@ def test_light_cache_gpu_kernel_matches_host(nx, monkeypatch):
         assert hashlib.sha256(struct.pack("<4096I", *c.l1_cache)).hexdigest() == e["l1_sha256_epoch0"]
     finally:
         c.close()
+
+
+def test_two_gpu_sharded_build_and_search(nx):
+    """Real N=2 path (NCCL all-gather of the DAG slices, sharded search) when the box has two GPUs."""
+    import subprocess
+    import sys
+
+    from conftest import ROOT
+    if nx.lib.nx_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533", "tools/multigpu_check.py"],
+                         cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert '"multigpu_check": "ok"' in out.stdout
