@@ -8,7 +8,7 @@ OBJ       := build/obj
 LIB       := $(PKG)/libnxkawpow.so
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function,-Wno-unknown-pragmas -Iinclude -I$(SRC)
-CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp
+CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp nx_compat.cpp
 CUSRC     := nx_dag.cu
 OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o))
 
@@ -22,11 +22,11 @@ $(SRC)/kawpow_kernel_src.inc: $(SRC)/kawpow_kernel.cuh
 
 $(OBJ)/nx_kernel_src.o: $(SRC)/kawpow_kernel_src.inc
 
-$(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h
+$(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h include/nx/ethash_compat.h include/nx/ethash_compat.hpp
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
 
-$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h
+$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h include/nx/ethash_compat.h include/nx/ethash_compat.hpp
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@
 

@@ -1,0 +1,2 @@
+/* forwards the reference include path to the nx drop-in */
+#include "../../../../nx/ethash_compat.h"

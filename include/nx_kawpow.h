@@ -204,6 +204,17 @@ typedef struct nx_verify_record
 int nx_kawpow_verify_batch(const nx_epoch* ctx, const nx_verify_record* records, size_t n, uint8_t* ok);
 
 /* ------------------------------------------------------------------------------------------------
+ * Classic Ethash (exported by the reference, no node caller; kernel K7).
+ * Replaces ethash_hash (crypto/ethash/lib/ethash/ethash.cpp:416-422, kernel :257-303) for one nonce or
+ * `count` consecutive nonces (out = count x {final_hash[32], mix_hash[32]}, HOST memory), and
+ * ethash_verify_final_hash (:424-429; host only, 1 = final hash <= boundary). */
+int nx_ethash_hash(const nx_epoch* ctx, const uint8_t header_hash[32], uint64_t nonce, nx_result* out);
+int nx_ethash_hash_batch(const nx_epoch* ctx, const uint8_t header_hash[32], uint64_t start_nonce, uint64_t count,
+                         uint8_t* out_host);
+int nx_ethash_verify_final_hash(const uint8_t header_hash[32], const uint8_t mix_hash[32], uint64_t nonce,
+                                const uint8_t boundary[32]);
+
+/* ------------------------------------------------------------------------------------------------
  * Node glue — host only. */
 
 /* header_hash that the node feeds to progpow: SHA256d over the 80-byte CKAWPOWInput

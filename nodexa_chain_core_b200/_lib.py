@@ -85,6 +85,9 @@ def _load() -> C.CDLL:
         "nx_kawpow_verify": (i, [vp, i, u8p, u8p, u64, u8p]),
         "nx_kawpow_hash_no_verify": (None, [i, u8p, u8p, u64, u8p]),
         "nx_kawpow_verify_batch": (i, [vp, C.POINTER(NxVerifyRecord), sz, u8p]),
+        "nx_ethash_hash": (i, [vp, u8p, u64, C.POINTER(NxResult)]),
+        "nx_ethash_hash_batch": (i, [vp, u8p, u64, u64, vp]),
+        "nx_ethash_verify_final_hash": (i, [u8p, u8p, u64, u8p]),
         "nx_kawpow_header_hash": (None, [C.c_int32, u8p, u8p, u32, u32, u32, u8p]),
         "nx_sha256d": (None, [u8p, sz, u8p]),
         "nx_compact_to_boundary": (i, [u32, u8p]),

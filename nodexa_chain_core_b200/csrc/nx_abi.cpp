@@ -144,7 +144,7 @@ int create(int epoch, int device, int rank, int world, nx_epoch** out)
     NX_TRY(cudaEventCreate(&c->ev1));
     NX_TRY(cudaMallocHost((void**)&c->light_host, light_bytes));
     NX_TRY(cudaMalloc(&c->light_dev, light_bytes));
-    NX_TRY(cudaMalloc(&c->dag_dev, c->dag_padded_bytes));
+    NX_TRY(cudaMalloc(&c->dag_dev, c->dag_padded_bytes + 256));  // +1 item: classic Ethash reaches 128-byte item n-1
     NX_TRY(cudaMalloc((void**)&c->found_min_dev, 2 * sizeof(uint64_t)));
     NX_TRY(cudaMallocHost((void**)&c->found_min_host, 2 * sizeof(uint64_t)));
     NX_TRY(cudaMalloc((void**)&c->checksum_partials_dev, CHECKSUM_PARTIALS * sizeof(uint64_t)));
@@ -218,6 +218,14 @@ int nx_epoch_finalize(nx_epoch* c)
     }
     std::lock_guard<std::mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
+    // KawPow addresses floor(n/2) 256-byte items; classic Ethash also reaches the odd last 128-byte item
+    // n-1, i.e. the first half of 256-byte item floor(n/2): generate that one item behind the rest.
+    {
+        const int rc = dag_generate(c->light_dev, c->light_items, c->dag_items, 1,
+                                    (char*)c->dag_dev + (size_t)c->dag_items * 256, c->stream);
+        if (rc != NX_OK) return rc;
+        NX_CUDA(cudaStreamSynchronize(c->stream));
+    }
     // L1 cache mirror = first 16 KiB of the DAG (reference ethash.cpp:168-170)
     NX_CUDA(cudaMemcpy(c->l1_host, c->dag_dev, sizeof c->l1_host, cudaMemcpyDeviceToHost));
     c->ready = true;
@@ -271,7 +279,7 @@ int nx_dag_read_items(const nx_epoch* c, uint32_t first, uint32_t count, uint8_t
         set_error("null argument");
         return NX_ERR_INVALID;
     }
-    if ((uint64_t)first + count > (uint64_t)c->share_items * c->world) {
+    if ((uint64_t)first + count > (uint64_t)c->share_items * c->world + 1) {  // +1: classic Ethash's extra item
         set_error("item range beyond the DAG buffer");
         return NX_ERR_INVALID;
     }
@@ -379,6 +387,56 @@ int nx_kawpow_hash(const nx_epoch* c, int block_number, const uint8_t header_has
     }
     uint8_t buf[64];
     const int rc = nx_kawpow_hash_batch(c, block_number, header_hash, nonce, 1, buf);
+    if (rc != NX_OK) return rc;
+    std::memcpy(out->final_hash, buf, 32);
+    std::memcpy(out->mix_hash, buf + 32, 32);
+    return NX_OK;
+}
+
+int nx_ethash_hash_batch(const nx_epoch* cc, const uint8_t header_hash[32], uint64_t start_nonce, uint64_t count,
+                         uint8_t* out_host)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    int rc = check_ctx(c, 0);
+    if (rc != NX_OK) return rc;
+    if (!header_hash || (!out_host && count)) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if (count == 0) return NX_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    constexpr uint64_t CHUNK = 1ull << 22;
+    if ((rc = ensure_batch_out(c, (size_t)(count < CHUNK ? count : CHUNK) * 64)) != NX_OK) return rc;
+    float total_ms = 0;
+    int launches = 0;
+    for (uint64_t done = 0; done < count; done += CHUNK) {
+        const uint64_t n = count - done < CHUNK ? count - done : CHUNK;
+        NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+        if ((rc = ethash_hash_batch(c->dag_dev, (uint32_t)c->dataset_items, header_hash, start_nonce + done, n,
+                                    c->batch_out_dev, c->stream)) != NX_OK)
+            return rc;
+        NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+        NX_CUDA(cudaMemcpyAsync(out_host + done * 64, c->batch_out_dev, (size_t)n * 64, cudaMemcpyDeviceToHost, c->stream));
+        NX_CUDA(cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        NX_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        total_ms += ms;
+        ++launches;
+    }
+    c->last_kernel_ms = total_ms;
+    c->last_launches = launches;
+    return NX_OK;
+}
+
+int nx_ethash_hash(const nx_epoch* c, const uint8_t header_hash[32], uint64_t nonce, nx_result* out)
+{
+    if (!out) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    uint8_t buf[64];
+    const int rc = nx_ethash_hash_batch(c, header_hash, nonce, 1, buf);
     if (rc != NX_OK) return rc;
     std::memcpy(out->final_hash, buf, 32);
     std::memcpy(out->mix_hash, buf + 32, 32);

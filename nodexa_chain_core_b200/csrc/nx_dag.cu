@@ -201,6 +201,70 @@ __global__ void light_cache_kernel(uint64_t* __restrict__ cache, uint32_t n, uin
         }
     }
 }
+// ---- classic Ethash hash (K7) ----
+// Replaces hash_seed / hash_kernel / hash_final (reference ethash.cpp:257-303) applied to a batch of
+// nonces.  The DAG is addressed as 128-byte items here (index_limit = full_dataset_num_items, :279).
+// No node caller exists for this function; one thread per nonce keeps it simple:
+// 64 dependent 128-byte reads = 8 192 B of DAG per hash.
+constexpr int ETHASH_THREADS = 128;
+__global__ void __launch_bounds__(ETHASH_THREADS)
+ethash_hash_kernel(const uint4* __restrict__ dag, uint32_t num_items_128, uint64_t h0, uint64_t h1, uint64_t h2,
+                   uint64_t h3, uint64_t start_nonce, uint64_t count, uint4* __restrict__ out)
+{
+    const uint64_t gid = (uint64_t)blockIdx.x * ETHASH_THREADS + threadIdx.x;
+    if (gid >= count) return;
+    uint64_t a[25];
+    a[0] = h0; a[1] = h1; a[2] = h2; a[3] = h3;
+    a[4] = start_nonce + gid;
+    a[5] = 0x01;  // 40-byte message: pad byte right after it
+#pragma unroll
+    for (int i = 6; i < 25; ++i) a[i] = 0;
+    a[8] = 0x8000000000000000ULL;  // rate 72 bytes
+    keccakf1600(a);
+    uint32_t seed[16], mix[32];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        seed[2 * i] = (uint32_t)a[i];
+        seed[2 * i + 1] = (uint32_t)(a[i] >> 32);
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) mix[i] = seed[i & 15];
+#pragma unroll 1
+    for (uint32_t i = 0; i < 64; i += 32) {
+#pragma unroll
+        for (uint32_t ii = 0; ii < 32; ++ii) {
+            const uint32_t p = fnv1((i + ii) ^ seed[0], mix[ii]) % num_items_128;
+            const uint4* src = dag + (size_t)p * 8;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const uint4 v = __ldg(src + q);
+                mix[4 * q] = fnv1(mix[4 * q], v.x);
+                mix[4 * q + 1] = fnv1(mix[4 * q + 1], v.y);
+                mix[4 * q + 2] = fnv1(mix[4 * q + 2], v.z);
+                mix[4 * q + 3] = fnv1(mix[4 * q + 3], v.w);
+            }
+        }
+    }
+    uint32_t mh[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) mh[i] = fnv1(fnv1(fnv1(mix[4 * i], mix[4 * i + 1]), mix[4 * i + 2]), mix[4 * i + 3]);
+    // final = keccak256(seed[64] || mix_hash[32]): 96 bytes, rate 136
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = (uint64_t)seed[2 * i] | ((uint64_t)seed[2 * i + 1] << 32);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a[8 + i] = (uint64_t)mh[2 * i] | ((uint64_t)mh[2 * i + 1] << 32);
+    a[12] = 0x01;
+#pragma unroll
+    for (int i = 13; i < 25; ++i) a[i] = 0;
+    a[16] = 0x8000000000000000ULL;
+    keccakf1600(a);
+    uint4* o = out + gid * 4;
+    o[0] = make_uint4((uint32_t)a[0], (uint32_t)(a[0] >> 32), (uint32_t)a[1], (uint32_t)(a[1] >> 32));
+    o[1] = make_uint4((uint32_t)a[2], (uint32_t)(a[2] >> 32), (uint32_t)a[3], (uint32_t)(a[3] >> 32));
+    o[2] = make_uint4(mh[0], mh[1], mh[2], mh[3]);
+    o[3] = make_uint4(mh[4], mh[5], mh[6], mh[7]);
+}
+
 // ---- allocation-free DAG checksum (see nx_dag_checksum_noalloc in include/nx_kawpow.h) ----
 // Same weighted sum as checksum_partial_kernel, but the per-CTA partial sums live in a fixed array
 // inside the library image instead of a buffer the context cudaMalloc'ed.  One CTA reduces one
@@ -321,6 +385,24 @@ int dag_generate(const void* light_dev, int light_items, uint32_t first_item256,
     const uint32_t blocks = (uint32_t)((count512 + DAG_THREADS - 1) / DAG_THREADS);
     dag_items_kernel<<<blocks, DAG_THREADS, 0, s>>>(static_cast<const uint4*>(light_dev), fm, first_item256 * 4u,
                                                     (uint32_t)count512, static_cast<uint4*>(out_dev));
+    NX_CUDA(cudaGetLastError());
+    return NX_OK;
+}
+
+int ethash_hash_batch(const void* dag_dev, uint32_t num_items_128, const uint8_t header[32], uint64_t start_nonce,
+                      uint64_t count, void* out_dev, cudaStream_t s)
+{
+    if (count == 0) return NX_OK;
+    uint64_t h[4];
+    memcpy(h, header, 32);
+    const uint64_t blocks = (count + ETHASH_THREADS - 1) / ETHASH_THREADS;
+    if (blocks > 0x7fffffffull) {
+        set_error("ethash batch too large");
+        return NX_ERR_INVALID;
+    }
+    ethash_hash_kernel<<<(unsigned)blocks, ETHASH_THREADS, 0, s>>>(static_cast<const uint4*>(dag_dev), num_items_128, h[0],
+                                                                  h[1], h[2], h[3], start_nonce, count,
+                                                                  static_cast<uint4*>(out_dev));
     NX_CUDA(cudaGetLastError());
     return NX_OK;
 }

@@ -194,6 +194,18 @@ void nx_kawpow_hash_no_verify(int block_number, const uint8_t header_hash[32], c
     std::memcpy(out, st, 32);
 }
 
+int nx_ethash_verify_final_hash(const uint8_t header_hash[32], const uint8_t mix_hash[32], uint64_t nonce,
+                                const uint8_t boundary[32])
+{
+    uint8_t init[40], fin[96], out[32];
+    std::memcpy(init, header_hash, 32);
+    std::memcpy(init + 32, &nonce, 8);
+    sponge(fin, 64, init, 40);
+    std::memcpy(fin + 64, mix_hash, 32);
+    sponge(out, 32, fin, 96);
+    return std::memcmp(out, boundary, 32) <= 0 ? 1 : 0;
+}
+
 void nx_sha256d(const uint8_t* data, size_t size, uint8_t out[32])
 {
     uint8_t first[32];

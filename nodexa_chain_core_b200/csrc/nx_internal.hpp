@@ -60,6 +60,8 @@ constexpr int KAWPOW_THREADS = 256;
 // ---- CUDA kernels (nx_dag.cu) ----
 int dag_generate(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256,
                  void* out_dev, cudaStream_t s);
+int ethash_hash_batch(const void* dag_dev, uint32_t num_items_128, const uint8_t header[32], uint64_t start_nonce,
+                      uint64_t count, void* out_dev, cudaStream_t s);
 int light_cache_build_gpu(void* light_dev, int light_items, const uint8_t seed[32], cudaStream_t s);
 int dag_checksum(const void* dag_dev, size_t n_words64, uint64_t* partials_dev, int n_partials, uint64_t* out_dev,
                  cudaStream_t s);

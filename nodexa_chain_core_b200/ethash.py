@@ -178,3 +178,29 @@ def create_epoch_context(epoch_number: int, device: int = 0) -> EpochContext:
 def create_epoch_context_full(epoch_number: int, device: int = 0) -> EpochContext:
     """ethash.hpp:117-120 / ethash.cpp:400-403"""
     return EpochContext(epoch_number, device)
+
+
+def hash(context: EpochContext, header_hash: bytes, nonce: int):  # noqa: A001
+    """ethash::hash / ethash_hash (ethash.cpp:306-324,416-422): classic Ethash, returns (final_hash, mix_hash)."""
+    from ._lib import NxResult
+    r = NxResult()
+    check(lib.nx_ethash_hash(context._h, inb(header_hash), nonce, C.byref(r)))
+    return bytes(r.final_hash), bytes(r.mix_hash)
+
+
+def hash_batch(context: EpochContext, header_hash: bytes, start_nonce: int, count: int) -> bytes:
+    out = outb(64 * count)
+    check(lib.nx_ethash_hash_batch(context._h, inb(header_hash), start_nonce, count, out))
+    return bytes(out)
+
+
+def verify_final_hash(header_hash: bytes, mix_hash: bytes, nonce: int, boundary: bytes) -> bool:
+    """ethash_verify_final_hash (ethash.cpp:424-429)"""
+    return bool(lib.nx_ethash_verify_final_hash(inb(header_hash), inb(mix_hash), nonce, inb(boundary)))
+
+
+def verify(context: EpochContext, header_hash: bytes, mix_hash: bytes, nonce: int, boundary: bytes) -> bool:
+    """ethash_verify (ethash.cpp:431-440): boundary test first, then the mix is recomputed."""
+    if not verify_final_hash(header_hash, mix_hash, nonce, boundary):
+        return False
+    return hash(context, header_hash, nonce)[1] == mix_hash

@@ -12,10 +12,10 @@ from conftest import ROOT
 
 def _declared_symbols():
     names = set()
-    for h in glob.glob(os.path.join(ROOT, "include", "*.h")):
+    for h in glob.glob(os.path.join(ROOT, "include", "*.h")) + glob.glob(os.path.join(ROOT, "include", "nx", "*.h")):
         txt = open(h).read()
         txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-        names |= set(re.findall(r"\b(nx_[a-z0-9_]+)\s*\(", txt))
+        names |= set(re.findall(r"\b((?:nx|ethash)_[a-z0-9_]+)\s*\(", txt))
     return names
 
 
@@ -23,8 +23,9 @@ def test_every_declared_symbol_is_exported(nx):
     declared = _declared_symbols()
     assert len(declared) > 40
     out = subprocess.check_output(["nm", "-D", "--defined-only", nx.LIB_PATH], text=True)
-    exported = set(re.findall(r" T (nx_[a-z0-9_]+)", out))
+    exported = set(re.findall(r" T ((?:nx|ethash)_[a-z0-9_]+)", out))
     assert declared <= exported, sorted(declared - exported)
+    assert "ethash_create_epoch_context" in declared and "nx_kawpow_search" in declared
     for name in declared:
         getattr(nx.lib, name)
 
