@@ -36,6 +36,37 @@ typedef unsigned long long u64;
 #ifndef NX_MIN_BLOCKS
 #define NX_MIN_BLOCKS 4
 #endif
+// Tunables set by the run-time (nx_kawpow_rt.cpp) through -D:
+//   NX_L1_COPIES  1|2|4|8  replicas of the 16 KiB L1 cache in shared memory.  Copy g is interleaved at a
+//                 word stride of NX_L1_COPIES, so it only occupies banks {g, g+C, g+2C, ...}; the lanes of a
+//                 warp are spread over the copies, which lowers the expected bank-conflict degree of the
+//                 random 4-byte reads (3.53 -> 2.96 for 8 copies) at the same instruction count.
+//   NX_ROT_IMAD   0..16    how many of every 16 constant rotates of the merge steps are done as a
+//                 32x32->64 multiply (FMA pipe) instead of a funnel shift (ALU pipe).
+//   NX_UNROLL     1|2|4    unroll factor of the 64-round loop.
+#ifndef NX_L1_COPIES
+#define NX_L1_COPIES 1
+#endif
+#ifndef NX_ROT_IMAD
+#define NX_ROT_IMAD 0
+#endif
+#ifndef NX_L1_HI
+#define NX_L1_HI 0
+#endif
+#ifndef NX_UNROLL
+#define NX_UNROLL 1
+#endif
+#if NX_L1_COPIES == 1
+#define NX_L1_LOG 0
+#elif NX_L1_COPIES == 2
+#define NX_L1_LOG 1
+#elif NX_L1_COPIES == 4
+#define NX_L1_LOG 2
+#elif NX_L1_COPIES == 8
+#define NX_L1_LOG 3
+#else
+#error "NX_L1_COPIES must be 1, 2, 4 or 8"
+#endif
 
 #define NX_FNV_PRIME 0x01000193u
 #define NX_FNV_BASIS 0x811c9dc5u
@@ -57,6 +88,25 @@ NX_DEV u32 nx_clz(u32 a) { return a ? (u32)__builtin_clz(a) : 32u; }
 NX_DEV u32 nx_popc(u32 a) { return (u32)__builtin_popcount(a); }
 #endif
 NX_DEV u32 nx_fnv1a(u32 h, u32 d) { return (h ^ d) * NX_FNV_PRIME; }
+
+// rotate by a literal 1..31 (merge steps); k is the ordinal of the rotate within the period program.
+// NX_ROT_IMAD = N (0..16) turns N out of every 16 of them, evenly spread, into a 32x32->64 multiply whose
+// halves are OR-ed (x*2^n = (x<<n) low, (x>>(32-n)) high): that is FMA-pipe work (at two issue slots per
+// wide multiply) taken off the busier ALU pipe.
+#if defined(__CUDACC__) && NX_ROT_IMAD
+NX_DEV u32 nx_rotl_c(u32 x, u32 n, u32 k)
+{
+    if (((k * NX_ROT_IMAD) >> 4) != (((k + 1u) * NX_ROT_IMAD) >> 4)) {
+        u32 lo, hi;
+        asm("{\n\t.reg .u64 p;\n\tmul.wide.u32 p, %2, %3;\n\tmov.b64 {%0, %1}, p;\n\t}" : "=r"(lo), "=r"(hi) : "r"(x), "r"(1u << n));
+        return lo | hi;
+    }
+    return nx_rotl(x, n);
+}
+#else
+NX_DEV u32 nx_rotl_c(u32 x, u32 n, u32 k) { (void)k; return nx_rotl(x, n); }
+#endif
+NX_DEV u32 nx_rotr_c(u32 x, u32 n, u32 k) { return nx_rotl_c(x, 32u - n, k); }
 
 // ---- KISS99 (reference lib/ethash/kiss99.hpp:31-62) ----
 struct NxKiss99
@@ -179,6 +229,25 @@ struct NxJob
 
 NX_DEV u32 nx_bswap(u32 x) { return __byte_perm(x, 0, 0x0123); }
 
+// one L1-cache word.  Address = lane_base + (x & 4095) * 4 * NX_L1_COPIES.
+//   default:    AND (ALU pipe) + multiply-add (FMA pipe) + LDS
+//   NX_L1_HI:   x*2^20 keeps only the low 12 bits of x; the high half of (that * 2^(14+log2 copies)) is the
+//               scaled index, so both steps run on the FMA pipe and the ALU pipe (the busier one) is spared.
+NX_DEV u32 nx_l1_load(u32 x, u32 lane_base)
+{
+    u32 v;
+#if NX_L1_HI
+    asm("{\n\t.reg .u32 t;\n\tmul.lo.u32 t, %1, 1048576;\n\tmad.hi.u32 t, t, %2, %3;\n\tld.shared.u32 %0, [t];\n\t}"
+        : "=r"(v)
+        : "r"(x), "n"(1 << (14 + NX_L1_LOG)), "r"(lane_base));
+#else
+    asm("{\n\t.reg .u32 t;\n\tand.b32 t, %1, 4095;\n\tmad.lo.u32 t, t, %2, %3;\n\tld.shared.u32 %0, [t];\n\t}"
+        : "=r"(v)
+        : "r"(x), "n"(4 * NX_L1_COPIES), "r"(lane_base));
+#endif
+    return v;
+}
+
 NX_DEV uint4 nx_ld_dag(const uint4* p)
 {
     uint4 v;
@@ -193,17 +262,34 @@ template <int MODE>
 NX_DEV void nx_kawpow_body(const uint4* __restrict__ dag, const NxJob& job, u32* __restrict__ out,
                            u64* __restrict__ found_min)
 {
-    __shared__ __align__(16) u32 l1s[4096];
-    __shared__ u32 carry_s[6][NX_THREADS];
-    __shared__ u32 digest_s[8][NX_THREADS];
+    // dynamic shared memory: [L1 cache, NX_L1_COPIES interleaved replicas][carry 6 x T][digest 8 x T]
+    extern __shared__ __align__(16) u32 nx_smem[];
+    u32* const l1s = nx_smem;
+    u32(*const carry_s)[NX_THREADS] = reinterpret_cast<u32(*)[NX_THREADS]>(nx_smem + 4096 * NX_L1_COPIES);
+    u32(*const digest_s)[NX_THREADS] = reinterpret_cast<u32(*)[NX_THREADS]>(nx_smem + 4096 * NX_L1_COPIES + 6 * NX_THREADS);
 
     const u32 tid = threadIdx.x;
+    // this lane's replica: word g of every interleaved group of NX_L1_COPIES words
+    u32 l1_rep = (tid & 31u) >> (5 - NX_L1_LOG);
+#if NX_L1_COPIES > 1
+    asm volatile("" : "+r"(l1_rep));  // keep it a plain register instead of re-deriving it from tid at each use
+#endif
+    // 32-bit shared-window address of word 0 of this lane's replica
+    const u32 l1_base = (u32)__cvta_generic_to_shared(l1s) + l1_rep * 4u;
     const u32 lane = tid & 15u;
     const u64 gid = (u64)blockIdx.x * NX_THREADS + tid;
     const u64 nonce = job.start_nonce + gid;
 
     // L1 cache = first 16 KiB of the DAG (reference ethash.cpp:168-170)
+#if NX_L1_COPIES == 1
     for (u32 i = tid; i < 1024u; i += NX_THREADS) reinterpret_cast<uint4*>(l1s)[i] = __ldg(dag + i);
+#else
+    for (u32 i = tid; i < 4096u; i += NX_THREADS) {
+        const u32 v = __ldg(reinterpret_cast<const u32*>(dag) + i);
+#pragma unroll
+        for (int g = 0; g < NX_L1_COPIES; ++g) l1s[i * NX_L1_COPIES + g] = v;
+    }
+#endif
 
     u32 seed0, seed1;
     {
@@ -226,12 +312,12 @@ NX_DEV void nx_kawpow_body(const uint4* __restrict__ dag, const NxJob& job, u32*
         u32 m[32];
         nx_fill_mix(__shfl_sync(0xffffffffu, seed0, h, 16), __shfl_sync(0xffffffffu, seed1, h, 16), lane, m);
 
-#pragma unroll 1
+#pragma unroll NX_UNROLL
         for (u32 r = 0; r < 64u; ++r) {
             // item index comes from lane r%16 (reference progpow.cpp:182-183)
             const u32 item = __shfl_sync(0xffffffffu, m[0], r & 15u, 16) % NX_DAG_ITEMS;
             const uint4 d = nx_ld_dag(dag + ((u64)item * 16u + ((lane ^ r) & 15u)));
-#define NX_L1(x) l1s[(x) & 4095u]
+#define NX_L1(x) nx_l1_load((x), l1_base)
             NX_ROUND_CACHE_MATH(m, NX_L1);
 #undef NX_L1
             NX_ROUND_DAG(m, d.x, d.y, d.z, d.w);

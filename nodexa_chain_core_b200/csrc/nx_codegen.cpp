@@ -64,15 +64,15 @@ std::string reg(const char* arr, uint32_t i)
 }
 
 // a = merge(a, b, sel)   (progpow.cpp:126-144)
-std::string merge_expr(const std::string& a, const std::string& b, uint32_t sel)
+std::string merge_expr(const std::string& a, const std::string& b, uint32_t sel, int& rot_ordinal)
 {
     const uint32_t x = ((sel >> 16) % 31) + 1;
     std::ostringstream s;
     switch (sel % 4) {
     case 0: s << a << " = " << a << " * 33u + " << b << ";"; break;
     case 1: s << a << " = (" << a << " ^ " << b << ") * 33u;"; break;
-    case 2: s << a << " = nx_rotl(" << a << ", " << x << "u) ^ " << b << ";"; break;
-    default: s << a << " = nx_rotr(" << a << ", " << x << "u) ^ " << b << ";"; break;
+    case 2: s << a << " = nx_rotl_c(" << a << ", " << x << "u, " << rot_ordinal++ << "u) ^ " << b << ";"; break;
+    default: s << a << " = nx_rotr_c(" << a << ", " << x << "u, " << rot_ordinal++ << "u) ^ " << b << ";"; break;
     }
     return s.str();
 }
@@ -139,19 +139,19 @@ std::string kawpow_program_text(uint64_t prog_seed)
     cm << "#define NX_ROUND_CACHE_MATH(m, L1) do { \\\n";
     dg << "#define NX_ROUND_DAG(m, d0, d1, d2, d3) do { \\\n";
     static const char* dag_words[4] = {"(d0)", "(d1)", "(d2)", "(d3)"};
-    int n = 0;
+    int n = 0, rot = 0;
     for (const ProgramOp& op : ops) {
         switch (op.kind) {
         case ProgramOp::CACHE:
             cm << "  { const u32 t" << n << " = L1(" << reg("m", op.src1) << "); "
-               << merge_expr(reg("m", op.dst), "t" + std::to_string(n), op.sel_merge) << " } \\\n";
+               << merge_expr(reg("m", op.dst), "t" + std::to_string(n), op.sel_merge, rot) << " } \\\n";
             break;
         case ProgramOp::MATH:
             cm << "  { const u32 t" << n << " = " << math_expr(reg("m", op.src1), reg("m", op.src2), op.sel_math) << "; "
-               << merge_expr(reg("m", op.dst), "t" + std::to_string(n), op.sel_merge) << " } \\\n";
+               << merge_expr(reg("m", op.dst), "t" + std::to_string(n), op.sel_merge, rot) << " } \\\n";
             break;
         case ProgramOp::DAG:
-            dg << "  " << merge_expr(reg("m", op.dst), dag_words[op.src1], op.sel_merge) << " \\\n";
+            dg << "  " << merge_expr(reg("m", op.dst), dag_words[op.src1], op.sel_merge, rot) << " \\\n";
             break;
         }
         ++n;

@@ -39,8 +39,50 @@ __device__ __forceinline__ uint32_t fast_mod(uint32_t x, FastMod f)
 
 constexpr int DAG_THREADS = 128;
 
-// One thread owns one 64-byte item for the two Keccak calls; the 512-parent FNV walk of each item
-// is done by the four lanes of its quad together (each lane holds 4 of the 16 mix words).
+// 4x4 exchange inside a lane quad.  Before: lane q holds the 16 mix words of ITS item in w[0..15].
+// After: lane s holds words 4s..4s+3 of all four items of the quad, a[q][c] = word 4s+c of lane q's item.
+// (And back again with the same pattern.)  Register indices must be literals, so the word group a lane
+// sends in step d - the one its partner s^d needs - is picked with selects.
+__device__ __forceinline__ void quad_scatter(const uint32_t w[16], uint32_t a[4][4], uint32_t sub)
+{
+#pragma unroll
+    for (uint32_t d = 0; d < 4; ++d) {
+        const uint32_t want = sub ^ d;  // my partner in this step, and the word group it needs from me
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const uint32_t send = want == 0 ? w[c] : want == 1 ? w[4 + c] : want == 2 ? w[8 + c] : w[12 + c];
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, send, d, 4);
+            // `got` is word 4*sub+c of lane (sub^d)'s item
+            if (want == 0) a[0][c] = got;
+            if (want == 1) a[1][c] = got;
+            if (want == 2) a[2][c] = got;
+            if (want == 3) a[3][c] = got;
+        }
+    }
+}
+
+__device__ __forceinline__ void quad_gather(const uint32_t a[4][4], uint32_t w[16], uint32_t sub)
+{
+#pragma unroll
+    for (uint32_t d = 0; d < 4; ++d) {
+        const uint32_t partner = sub ^ d;  // I hold words 4*sub.. of partner's item in a[partner][*]
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const uint32_t send = partner == 0 ? a[0][c] : partner == 1 ? a[1][c] : partner == 2 ? a[2][c] : a[3][c];
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, send, d, 4);
+            // `got` is word 4*partner+c of MY item
+            if (partner == 0) w[c] = got;
+            if (partner == 1) w[4 + c] = got;
+            if (partner == 2) w[8 + c] = got;
+            if (partner == 3) w[12 + c] = got;
+        }
+    }
+}
+
+// One thread owns one 64-byte item for the two Keccak calls.  The 512-parent FNV walk is done by the four
+// lanes of a quad for their four items AT THE SAME TIME: lane s holds words 4s..4s+3 of each item, so every
+// step issues four independent 16-byte loads per lane (64 contiguous bytes per parent across the quad).
+// Four parents in flight per lane is what hides the L2 latency of the gather.
 __global__ void __launch_bounds__(DAG_THREADS)
 dag_items_kernel(const uint4* __restrict__ light, FastMod fm, uint32_t first512, uint32_t count512,
                  uint4* __restrict__ out)
@@ -69,43 +111,33 @@ dag_items_kernel(const uint4* __restrict__ light, FastMod fm, uint32_t first512,
         }
     }
 
+    uint32_t a[4][4];
+    quad_scatter(mix, a, sub);
+    uint32_t seed[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) seed[q] = __shfl_sync(0xffffffffu, k, q, 4);
+
 #pragma unroll 1
-    for (uint32_t p = 0; p < 4; ++p) {
-        const uint32_t seed = __shfl_sync(0xffffffffu, k, p, 4);
-        // lane `sub` takes words 4*sub..4*sub+3 of quad-lane p's item
-        uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+    for (uint32_t j = 0; j < 512; j += 16) {
 #pragma unroll
-        for (int w = 0; w < 16; ++w) {
-            const uint32_t v = __shfl_sync(0xffffffffu, mix[w], p, 4);
-            if ((uint32_t)(w >> 2) == sub) {
-                if ((w & 3) == 0) m0 = v;
-                if ((w & 3) == 1) m1 = v;
-                if ((w & 3) == 2) m2 = v;
-                if ((w & 3) == 3) m3 = v;
+        for (uint32_t jj = 0; jj < 16; ++jj) {
+            // mix word jj of every item lives in quad-lane jj/4, component jj%4
+            uint4 pv[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t t = fnv1(seed[q] ^ (j + jj), __shfl_sync(0xffffffffu, a[q][jj & 3], jj >> 2, 4));
+                pv[q] = __ldg(light + (size_t)fast_mod(t, fm) * 4 + sub);
             }
-        }
-#pragma unroll 1
-        for (uint32_t j = 0; j < 512; j += 16) {
 #pragma unroll
-            for (uint32_t jj = 0; jj < 16; ++jj) {
-                // mix word jj lives in quad-lane jj/4, component jj%4
-                const uint32_t mine = (jj & 3) == 0 ? m0 : (jj & 3) == 1 ? m1 : (jj & 3) == 2 ? m2 : m3;
-                const uint32_t t = fnv1(seed ^ (j + jj), __shfl_sync(0xffffffffu, mine, jj >> 2, 4));
-                const uint4 pv = __ldg(light + (size_t)fast_mod(t, fm) * 4 + sub);
-                m0 = fnv1(m0, pv.x);
-                m1 = fnv1(m1, pv.y);
-                m2 = fnv1(m2, pv.z);
-                m3 = fnv1(m3, pv.w);
+            for (int q = 0; q < 4; ++q) {
+                a[q][0] = fnv1(a[q][0], pv[q].x);
+                a[q][1] = fnv1(a[q][1], pv[q].y);
+                a[q][2] = fnv1(a[q][2], pv[q].z);
+                a[q][3] = fnv1(a[q][3], pv[q].w);
             }
-        }
-        // hand the 16 words back to quad-lane p
-#pragma unroll
-        for (int w = 0; w < 16; ++w) {
-            const uint32_t mine = (w & 3) == 0 ? m0 : (w & 3) == 1 ? m1 : (w & 3) == 2 ? m2 : m3;
-            const uint32_t v = __shfl_sync(0xffffffffu, mine, w >> 2, 4);
-            if (sub == p) mix[w] = v;
         }
     }
+    quad_gather(a, mix, sub);
 
     {
         uint64_t w[8];
@@ -113,11 +145,12 @@ dag_items_kernel(const uint4* __restrict__ light, FastMod fm, uint32_t first512,
         for (int i = 0; i < 8; ++i) w[i] = (uint64_t)mix[2 * i] | ((uint64_t)mix[2 * i + 1] << 32);
         keccak512_64(w);
         if (live) {
+            // streaming stores: the DAG is written once and must not push the light cache out of L2
             uint4* dst = out + (size_t)gid * 4;
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                dst[i] = make_uint4((uint32_t)w[2 * i], (uint32_t)(w[2 * i] >> 32), (uint32_t)w[2 * i + 1],
-                                    (uint32_t)(w[2 * i + 1] >> 32));
+                __stcs(dst + i, make_uint4((uint32_t)w[2 * i], (uint32_t)(w[2 * i] >> 32), (uint32_t)w[2 * i + 1],
+                                           (uint32_t)(w[2 * i + 1] >> 32)));
         }
     }
 }

@@ -55,7 +55,6 @@ int kawpow_compile_only(uint64_t prog_seed, uint32_t dag_items_256, std::vector<
 int kawpow_launch_hash(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* out_dev, cudaStream_t s);
 int kawpow_launch_search(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* found_min_dev,
                          cudaStream_t s);
-constexpr int KAWPOW_THREADS = 256;
 
 // ---- CUDA kernels (nx_dag.cu) ----
 int dag_generate(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256,

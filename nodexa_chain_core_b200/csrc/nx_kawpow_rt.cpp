@@ -69,12 +69,56 @@ const char* cu_err(CUresult_ r)
     return s ? s : "unknown driver error";
 }
 
+// Kernel shape.  Defaults are the measured best on B200; NX_KAWPOW_TUNE overrides them,
+// e.g. NX_KAWPOW_TUNE="copies=8,threads=1024,minblocks=1,rotimad=1".  Read once per process.
+struct Tune
+{
+    int copies = 1, threads = 256, minblocks = 4, rotimad = 0, l1hi = 0, unroll = 1;
+    size_t smem_bytes() const { return (size_t)copies * 16384 + (size_t)14 * 4 * threads; }
+    std::string tag() const
+    {
+        std::ostringstream s;
+        s << "c" << copies << "t" << threads << "b" << minblocks << "r" << rotimad << "h" << l1hi << "u" << unroll;
+        return s.str();
+    }
+};
+
+const Tune& tune()
+{
+    static Tune t;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char* e = std::getenv("NX_KAWPOW_TUNE");
+        if (!e) return;
+        std::string str(e);
+        size_t pos = 0;
+        while (pos < str.size()) {
+            size_t end = str.find(',', pos);
+            if (end == std::string::npos) end = str.size();
+            const std::string kv = str.substr(pos, end - pos);
+            const size_t eq = kv.find('=');
+            if (eq != std::string::npos) {
+                const std::string k = kv.substr(0, eq);
+                const int v = std::atoi(kv.c_str() + eq + 1);
+                if (k == "copies" && (v == 1 || v == 2 || v == 4 || v == 8)) t.copies = v;
+                if (k == "threads" && v >= 32 && v <= 1024 && v % 32 == 0) t.threads = v;
+                if (k == "minblocks" && v >= 1 && v <= 8) t.minblocks = v;
+                if (k == "rotimad" && v >= 0 && v <= 16) t.rotimad = v;
+                if (k == "l1hi") t.l1hi = v ? 1 : 0;
+                if (k == "unroll" && (v == 1 || v == 2 || v == 4 || v == 8)) t.unroll = v;
+            }
+            pos = end + 1;
+        }
+    });
+    return t;
+}
+
 std::string cache_path(uint64_t prog_seed, uint32_t dag_items, const char* arch)
 {
     const char* dir = std::getenv("NX_PROGRAM_CACHE_DIR");
     if (!dir || !*dir) return "";
     std::ostringstream s;
-    s << dir << "/kawpow_" << arch << "_" << prog_seed << "_" << dag_items << "_v1.cubin";
+    s << dir << "/kawpow_" << arch << "_" << prog_seed << "_" << dag_items << "_" << tune().tag() << "_v2.cubin";
     return s.str();
 }
 }  // namespace
@@ -88,6 +132,8 @@ struct KawpowProgram
     CUfunction_ fn_hash = nullptr, fn_search = nullptr;
     double compile_ms = 0;
     int regs_hash = 0, regs_search = 0;
+    int threads = 256;
+    size_t smem_bytes = 0;
     ~KawpowProgram();
 };
 
@@ -111,7 +157,16 @@ int compile_cubin(uint64_t prog_seed, uint32_t dag_items, std::vector<char>& cub
     }
     const char* arch_env = std::getenv("NX_KAWPOW_ARCH");
     const std::string arch = std::string("--gpu-architecture=") + (arch_env && *arch_env ? arch_env : "sm_100a");
-    std::vector<const char*> opts = {arch.c_str(), "--std=c++17", "-lineinfo", "--extra-device-vectorization"};
+    const Tune& tn = tune();
+    const std::string d_threads = "-DNX_THREADS=" + std::to_string(tn.threads);
+    const std::string d_blocks = "-DNX_MIN_BLOCKS=" + std::to_string(tn.minblocks);
+    const std::string d_copies = "-DNX_L1_COPIES=" + std::to_string(tn.copies);
+    const std::string d_rot = "-DNX_ROT_IMAD=" + std::to_string(tn.rotimad);
+    const std::string d_hi = "-DNX_L1_HI=" + std::to_string(tn.l1hi);
+    const std::string d_unroll = "-DNX_UNROLL=" + std::to_string(tn.unroll);
+    std::vector<const char*> opts = {arch.c_str(), "--std=c++17", "-lineinfo", "--extra-device-vectorization",
+                                     d_threads.c_str(), d_blocks.c_str(), d_copies.c_str(), d_rot.c_str(),
+                                     d_hi.c_str(), d_unroll.c_str()};
     std::vector<std::string> extra;
     if (const char* e = std::getenv("NX_KAWPOW_NVRTC_FLAGS")) {  // space separated, for experiments
         std::istringstream is(e);
@@ -198,14 +253,25 @@ int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
         set_error("cuModuleGetFunction failed: %s", cu_err(r));
         return NX_ERR_CUDA;
     }
+    p->threads = tune().threads;
+    p->smem_bytes = tune().smem_bytes();
+    if (p->smem_bytes > 48 * 1024) {
+        if (!d.FuncSetAttribute ||
+            (r = d.FuncSetAttribute(p->fn_hash, 8 /*CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES*/, (int)p->smem_bytes)) != 0 ||
+            (r = d.FuncSetAttribute(p->fn_search, 8, (int)p->smem_bytes)) != 0) {
+            set_error("cuFuncSetAttribute(max dynamic shared memory = %zu) failed: %s", p->smem_bytes, cu_err(r));
+            return NX_ERR_CUDA;
+        }
+    }
     if (d.FuncGetAttribute) {
         d.FuncGetAttribute(&p->regs_hash, 4 /*CU_FUNC_ATTRIBUTE_NUM_REGS*/, p->fn_hash);
         d.FuncGetAttribute(&p->regs_search, 4, p->fn_search);
     }
     p->compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (std::getenv("NX_VERBOSE"))
-        fprintf(stderr, "[nx] kawpow program seed=%llu items=%u: %.1f ms, regs hash=%d search=%d\n",
-                (unsigned long long)prog_seed, dag_items, p->compile_ms, p->regs_hash, p->regs_search);
+        fprintf(stderr, "[nx] kawpow program seed=%llu items=%u tune=%s: %.1f ms, regs hash=%d search=%d smem=%zu\n",
+                (unsigned long long)prog_seed, dag_items, tune().tag().c_str(), p->compile_ms, p->regs_hash,
+                p->regs_search, p->smem_bytes);
     // keep the cache bounded: a node only needs the current and the next period.  Evicted programs
     // are unloaded when their last user lets go of the shared_ptr.
     if (g_cache.size() >= 32) g_cache.clear();
@@ -214,16 +280,18 @@ int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
     return NX_OK;
 }
 
-static int launch(CUfunction_ fn, const void* dag, const KawpowJob& job, void* third, cudaStream_t s)
+static int launch(const KawpowProgram* p, CUfunction_ fn, const void* dag, const KawpowJob& job, void* third,
+                  cudaStream_t s)
 {
     if (job.count == 0) return NX_OK;
-    const uint64_t blocks = (job.count + KAWPOW_THREADS - 1) / KAWPOW_THREADS;
+    const uint64_t blocks = (job.count + p->threads - 1) / p->threads;
     if (blocks > 0x7fffffffull) {
         set_error("kawpow launch: batch of %llu nonces is too large for one grid", (unsigned long long)job.count);
         return NX_ERR_INVALID;
     }
     void* args[3] = {(void*)&dag, (void*)&job, (void*)&third};
-    const CUresult_ r = driver().LaunchKernel(fn, (unsigned)blocks, 1, 1, KAWPOW_THREADS, 1, 1, 0, (void*)s, args, nullptr);
+    const CUresult_ r = driver().LaunchKernel(fn, (unsigned)blocks, 1, 1, (unsigned)p->threads, 1, 1,
+                                              (unsigned)p->smem_bytes, (void*)s, args, nullptr);
     if (r != 0) {
         set_error("cuLaunchKernel failed: %s", cu_err(r));
         return NX_ERR_CUDA;
@@ -233,12 +301,12 @@ static int launch(CUfunction_ fn, const void* dag, const KawpowJob& job, void* t
 
 int kawpow_launch_hash(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* out_dev, cudaStream_t s)
 {
-    return launch(p->fn_hash, dag, job, out_dev, s);
+    return launch(p, p->fn_hash, dag, job, out_dev, s);
 }
 
 int kawpow_launch_search(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* found_min_dev, cudaStream_t s)
 {
-    return launch(p->fn_search, dag, job, found_min_dev, s);
+    return launch(p, p->fn_search, dag, job, found_min_dev, s);
 }
 
 }  // namespace nx

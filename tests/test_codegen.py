@@ -49,7 +49,7 @@ def test_program_matches_survey_appendix(nx):
     k, s1, s2, dst, selm, sel = ops[1]
     assert (k, s1, s2, selm % 11, dst, sel % 4) == (1, 21, 14, 3, 31, 0)
     txt = _source(nx, 0, 4194296, 0)
-    assert "m[18] = nx_rotr(m[18], 6u) ^ t0" in txt and "nx_min(m[21], m[14])" in txt
+    assert "m[18] = nx_rotr_c(m[18], 6u, 0u) ^ t0" in txt and "nx_min(m[21], m[14])" in txt
 
 
 @pytest.mark.parametrize("height", [0, 3, 49 * 3, 7499])
