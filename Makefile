@@ -9,7 +9,7 @@ LIB       := $(PKG)/libnxkawpow.so
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function,-Wno-unknown-pragmas -Iinclude -I$(SRC)
 CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp nx_compat.cpp
-CUSRC     := nx_dag.cu
+CUSRC     := nx_dag.cu nx_kawpow_interp.cu
 OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o))
 
 .PHONY: all lib oracle ref clean
@@ -21,6 +21,7 @@ $(SRC)/kawpow_kernel_src.inc: $(SRC)/kawpow_kernel.cuh
 	( printf 'R"NXSRC(' ; cat $< ; printf ')NXSRC"\n' ) > $@
 
 $(OBJ)/nx_kernel_src.o: $(SRC)/kawpow_kernel_src.inc
+$(OBJ)/nx_kawpow_interp.o: $(SRC)/kawpow_kernel.cuh
 
 $(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h include/nx/ethash_compat.h include/nx/ethash_compat.hpp
 	@mkdir -p $(OBJ)

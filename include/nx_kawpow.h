@@ -188,6 +188,19 @@ int nx_kawpow_verify(const nx_epoch* ctx, int block_number, const uint8_t header
 void nx_kawpow_hash_no_verify(int block_number, const uint8_t header_hash[32], const uint8_t mix_hash[32],
                               uint64_t nonce, uint8_t out[32]);
 
+/* Many independent records, each with its own header, nonce and height (any mix of ProgPoW periods inside
+ * the context's epoch): out_host = n x {final_hash[32], mix_hash[32]}.  Runs the interpreted kernel K6, which
+ * needs no per-period compilation - the shape of header validation, where every block is its own period.
+ * Replaces progpow::hash called once per header (validation.cpp:11652-11662, rpc/mining.cpp:811,880). */
+typedef struct nx_hash_record
+{
+    int32_t block_number;
+    uint32_t pad;
+    uint64_t nonce;
+    uint8_t header_hash[32];
+} nx_hash_record;
+int nx_kawpow_hash_many(const nx_epoch* ctx, const nx_hash_record* records, size_t n, uint8_t* out_host);
+
 /* Batched header verification (kernel K6): n independent {block_number(all in ctx's epoch), header,
  * mix, nonce, boundary} records; ok[i] = 1/0.  Replaces the per-header progpow::verify calls of
  * validation.cpp:11652-11662 during header sync.  Records are 112 bytes:

@@ -30,6 +30,10 @@ class NxSearchResult(C.Structure):
                 ("final_hash", C.c_uint8 * 32), ("mix_hash", C.c_uint8 * 32)]
 
 
+class NxHashRecord(C.Structure):
+    _fields_ = [("block_number", C.c_int32), ("pad", C.c_uint32), ("nonce", C.c_uint64), ("header_hash", C.c_uint8 * 32)]
+
+
 class NxVerifyRecord(C.Structure):
     _fields_ = [("block_number", C.c_int32), ("pad", C.c_uint32), ("nonce", C.c_uint64),
                 ("header_hash", C.c_uint8 * 32), ("mix_hash", C.c_uint8 * 32), ("boundary", C.c_uint8 * 32)]
@@ -84,6 +88,7 @@ def _load() -> C.CDLL:
         "nx_kawpow_last_timing": (i, [vp, C.POINTER(C.c_float), C.POINTER(i)]),
         "nx_kawpow_verify": (i, [vp, i, u8p, u8p, u64, u8p]),
         "nx_kawpow_hash_no_verify": (None, [i, u8p, u8p, u64, u8p]),
+        "nx_kawpow_hash_many": (i, [vp, C.POINTER(NxHashRecord), sz, vp]),
         "nx_kawpow_verify_batch": (i, [vp, C.POINTER(NxVerifyRecord), sz, u8p]),
         "nx_ethash_hash": (i, [vp, u8p, u64, C.POINTER(NxResult)]),
         "nx_ethash_hash_batch": (i, [vp, u8p, u64, u64, vp]),

@@ -215,7 +215,7 @@ NX_DEV void nx_keccakf800(u32 a[25])
     st[16] = 0x72u; st[17] = 0x41u; st[18] = 0x56u; st[19] = 0x45u; st[20] = 0x4Eu; st[21] = 0x43u;       \
     st[22] = 0x4Fu; st[23] = 0x49u; st[24] = 0x4Eu
 
-#ifdef __CUDACC__
+#if defined(__CUDACC__) && !defined(NX_HELPERS_ONLY)
 // ------------------------------------------------------------------------------------------ device
 
 struct NxJob
@@ -380,4 +380,4 @@ nx_kawpow_search_kernel(const uint4* __restrict__ dag, const NxJob job, u64* __r
 {
     nx_kawpow_body<1>(dag, job, nullptr, found_min);
 }
-#endif  // __CUDACC__
+#endif  // __CUDACC__ && !NX_HELPERS_ONLY

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <vector>
 #include <new>
 
 using namespace nx;
@@ -80,6 +81,7 @@ void destroy(nx_epoch* c)
     if (c->found_min_dev) cudaFree(c->found_min_dev);
     if (c->checksum_partials_dev) cudaFree(c->checksum_partials_dev);
     if (c->batch_out_dev) cudaFree(c->batch_out_dev);
+    if (c->many_dev) cudaFree(c->many_dev);
     if (c->found_min_host) cudaFreeHost(c->found_min_host);
     if (c->light_host) cudaFreeHost(c->light_host);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -386,7 +388,25 @@ int nx_kawpow_hash(const nx_epoch* c, int block_number, const uint8_t header_has
         return NX_ERR_INVALID;
     }
     uint8_t buf[64];
-    const int rc = nx_kawpow_hash_batch(c, block_number, header_hash, nonce, 1, buf);
+    int rc = check_ctx(c, block_number);
+    if (rc != NX_OK) return rc;
+    if (!header_hash) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    // A one-off hash (the node's verify path) does not wait for NVRTC: unless this period's program is
+    // already compiled, it goes through the interpreted kernel.
+    if (kawpow_program_is_cached(c->device, (uint64_t)(block_number / NX_PERIOD_LENGTH), c->dag_items) ||
+        block_number / NX_EPOCH_LENGTH != c->epoch) {
+        rc = nx_kawpow_hash_batch(c, block_number, header_hash, nonce, 1, buf);
+    } else {
+        nx_hash_record r;
+        r.block_number = block_number;
+        r.pad = 0;
+        r.nonce = nonce;
+        std::memcpy(r.header_hash, header_hash, 32);
+        rc = nx_kawpow_hash_many(c, &r, 1, buf);
+    }
     if (rc != NX_OK) return rc;
     std::memcpy(out->final_hash, buf, 32);
     std::memcpy(out->mix_hash, buf + 32, 32);
@@ -575,20 +595,101 @@ int nx_kawpow_verify(const nx_epoch* c, int block_number, const uint8_t header_h
     return std::memcmp(r.mix_hash, mix_hash, 32) == 0 ? 1 : 0;
 }
 
+int nx_kawpow_hash_many(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    int rc = check_ctx(c, 0);
+    if (rc != NX_OK) return rc;
+    if ((!records || !out_host) && n) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if (n == 0) return NX_OK;
+    if (n > 0x7fffffffu / 16) {
+        set_error("too many records in one call");
+        return NX_ERR_INVALID;
+    }
+    // one packed program per distinct period in the batch
+    std::map<uint64_t, uint32_t> slot_of;
+    std::vector<KawpowRecord> recs(n);
+    for (size_t i = 0; i < n; ++i) {
+        const int bn = records[i].block_number;
+        if (bn < 0 || bn / NX_EPOCH_LENGTH != c->epoch) {
+            set_error("record %zu: block %d is not in this context's epoch %d", i, bn, c->epoch);
+            return NX_ERR_INVALID;
+        }
+        const uint64_t seed = (uint64_t)(bn / NX_PERIOD_LENGTH);
+        auto it = slot_of.find(seed);
+        if (it == slot_of.end()) it = slot_of.emplace(seed, (uint32_t)slot_of.size()).first;
+        std::memcpy(recs[i].header, records[i].header_hash, 32);
+        recs[i].nonce = records[i].nonce;
+        recs[i].program_slot = it->second;
+        recs[i].pad = 0;
+    }
+    std::vector<uint32_t> progs(slot_of.size() * 36 * 4);
+    for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);
+
+    std::lock_guard<std::mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    const size_t rec_bytes = (n * sizeof(KawpowRecord) + 255) & ~(size_t)255;
+    const size_t prog_bytes = (progs.size() * 4 + 255) & ~(size_t)255;
+    const size_t need = rec_bytes + prog_bytes;
+    if (c->many_bytes < need) {
+        if (c->many_dev) cudaFree(c->many_dev);
+        c->many_dev = nullptr;
+        c->many_bytes = 0;
+        if (cudaMalloc(&c->many_dev, need) != cudaSuccess) {
+            cudaGetLastError();
+            set_error("out of device memory for %zu record bytes", need);
+            return NX_ERR_OOM;
+        }
+        c->many_bytes = need;
+    }
+    if ((rc = ensure_batch_out(c, n * 64)) != NX_OK) return rc;
+    char* base = static_cast<char*>(c->many_dev);
+    NX_CUDA(cudaMemcpyAsync(base, recs.data(), n * sizeof(KawpowRecord), cudaMemcpyHostToDevice, c->stream));
+    NX_CUDA(cudaMemcpyAsync(base + rec_bytes, progs.data(), progs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+    if ((rc = kawpow_interp_launch(c->dag_dev, c->dag_items, reinterpret_cast<const KawpowRecord*>(base), (uint32_t)n,
+                                   base + rec_bytes, c->batch_out_dev, c->stream)) != NX_OK)
+        return rc;
+    NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+    NX_CUDA(cudaMemcpyAsync(out_host, c->batch_out_dev, n * 64, cudaMemcpyDeviceToHost, c->stream));
+    NX_CUDA(cudaStreamSynchronize(c->stream));  // recs/progs are pageable host vectors: keep them alive until here
+    NX_CUDA(cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1));
+    c->last_launches = 1;
+    return NX_OK;
+}
+
 int nx_kawpow_verify_batch(const nx_epoch* c, const nx_verify_record* records, size_t n, uint8_t* ok)
 {
     if ((!records || !ok) && n) {
         set_error("null argument");
         return NX_ERR_INVALID;
     }
-    // Records that fail the boundary test never reach the GPU.  The rest are hashed one launch per
-    // record for now (each has its own header); K6 proper batches them per period.
+    // progpow::verify's order (progpow.cpp:487-494): the cheap final-hash-vs-boundary test on the host first;
+    // only records that pass it have their mix recomputed, all in one interpreted-kernel launch (K6).
+    std::vector<nx_hash_record> todo;
+    std::vector<size_t> index;
     for (size_t i = 0; i < n; ++i) {
-        const int v = nx_kawpow_verify(c, records[i].block_number, records[i].header_hash, records[i].mix_hash,
-                                       records[i].nonce, records[i].boundary);
-        if (v < 0) return v;
-        ok[i] = (uint8_t)v;
+        uint8_t fin[32];
+        nx_kawpow_hash_no_verify(records[i].block_number, records[i].header_hash, records[i].mix_hash, records[i].nonce, fin);
+        ok[i] = 0;
+        if (std::memcmp(fin, records[i].boundary, 32) > 0) continue;
+        nx_hash_record r;
+        r.block_number = records[i].block_number;
+        r.pad = 0;
+        r.nonce = records[i].nonce;
+        std::memcpy(r.header_hash, records[i].header_hash, 32);
+        todo.push_back(r);
+        index.push_back(i);
     }
+    if (todo.empty()) return check_ctx(c, 0);
+    std::vector<uint8_t> out(todo.size() * 64);
+    const int rc = nx_kawpow_hash_many(c, todo.data(), todo.size(), out.data());
+    if (rc != NX_OK) return rc;
+    for (size_t k = 0; k < todo.size(); ++k)
+        ok[index[k]] = std::memcmp(out.data() + 64 * k + 32, records[index[k]].mix_hash, 32) == 0 ? 1 : 0;
     return NX_OK;
 }
 

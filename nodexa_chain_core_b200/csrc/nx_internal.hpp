@@ -56,6 +56,19 @@ int kawpow_launch_hash(const KawpowProgram* p, const void* dag, const KawpowJob&
 int kawpow_launch_search(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* found_min_dev,
                          cudaStream_t s);
 
+// ---- interpreted KawPow for independent records (nx_kawpow_interp.cu, kernel K6) ----
+struct KawpowRecord
+{
+    uint32_t header[8];
+    uint64_t nonce;
+    uint32_t program_slot;  // index into the packed program table of this launch
+    uint32_t pad;
+};
+void kawpow_pack_program(uint64_t prog_seed, uint32_t out[36 * 4]);
+int kawpow_interp_launch(const void* dag, uint32_t dag_items, const KawpowRecord* recs_dev, uint32_t n_recs,
+                         const void* programs_dev, void* out_dev, cudaStream_t s);
+bool kawpow_program_is_cached(int device, uint64_t prog_seed, uint32_t dag_items_256);
+
 // ---- CUDA kernels (nx_dag.cu) ----
 int dag_generate(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256,
                  void* out_dev, cudaStream_t s);
@@ -92,6 +105,8 @@ struct nx_epoch
     uint64_t* checksum_partials_dev = nullptr;
     void* batch_out_dev = nullptr;
     size_t batch_out_bytes = 0;
+    void* many_dev = nullptr;  // records + packed programs of nx_kawpow_hash_many
+    size_t many_bytes = 0;
     // bookkeeping for enqueue/sync
     uint64_t pending_base = 0;  // start nonce that offset 0 of found_min refers to
     bool pending = false;

@@ -205,6 +205,12 @@ int kawpow_compile_only(uint64_t prog_seed, uint32_t dag_items, std::vector<char
     return compile_cubin(prog_seed, dag_items, cubin, log);
 }
 
+bool kawpow_program_is_cached(int device, uint64_t prog_seed, uint32_t dag_items)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    return g_cache.count(std::make_tuple(device, prog_seed, dag_items)) != 0;
+}
+
 int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<KawpowProgram>* out)
 {
     std::lock_guard<std::mutex> lk(g_cache_mu);

@@ -5,7 +5,7 @@ from __future__ import annotations
 import ctypes as C
 from dataclasses import dataclass
 
-from ._lib import NxResult, NxSearchResult, check, inb, lib, outb
+from ._lib import NxHashRecord, NxResult, NxSearchResult, NxVerifyRecord, check, inb, lib, outb
 from .ethash import EpochContext
 
 revision = "0.9.4"
@@ -98,3 +98,34 @@ def search_sync(context: EpochContext) -> SearchResult:
 
 def prepare(context: EpochContext, block_number: int) -> None:
     check(lib.nx_kawpow_prepare(context._h, block_number))
+
+
+def hash_many(context: EpochContext, records) -> list:
+    """records = iterable of (block_number, header_hash, nonce), any mix of periods inside the context's epoch.
+    One launch of the interpreted kernel (K6); returns [Result, ...]."""
+    records = list(records)
+    arr = (NxHashRecord * max(1, len(records)))()
+    for i, (bn, hd, nonce) in enumerate(records):
+        arr[i].block_number = bn
+        arr[i].nonce = nonce
+        C.memmove(arr[i].header_hash, hd, 32)
+    out = outb(64 * len(records))
+    check(lib.nx_kawpow_hash_many(context._h, arr, len(records), out))
+    b = bytes(out)
+    return [Result(b[64 * i:64 * i + 32], b[64 * i + 32:64 * i + 64]) for i in range(len(records))]
+
+
+def verify_batch(context: EpochContext, records) -> list:
+    """records = iterable of (block_number, header_hash, mix_hash, nonce, boundary); returns [bool, ...]
+    with progpow::verify's semantics for each (header sync: validation.cpp:11652-11662)."""
+    records = list(records)
+    arr = (NxVerifyRecord * max(1, len(records)))()
+    for i, (bn, hd, mix, nonce, boundary) in enumerate(records):
+        arr[i].block_number = bn
+        arr[i].nonce = nonce
+        C.memmove(arr[i].header_hash, hd, 32)
+        C.memmove(arr[i].mix_hash, mix, 32)
+        C.memmove(arr[i].boundary, boundary, 32)
+    ok = outb(max(1, len(records)))
+    check(lib.nx_kawpow_verify_batch(context._h, arr, len(records), ok))
+    return [bool(ok[i]) for i in range(len(records))]
