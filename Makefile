@@ -8,7 +8,7 @@ OBJ       := build/obj
 LIB       := $(PKG)/libnxkawpow.so
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function,-Wno-unknown-pragmas -Iinclude -I$(SRC)
-CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp nx_compat.cpp
+CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp nx_compat.cpp nx_miner.cpp
 CUSRC     := nx_dag.cu nx_kawpow_interp.cu
 OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o))
 

@@ -69,6 +69,10 @@ typedef struct nx_epoch nx_epoch;
 /* Light cache (CUDA kernel K4 or host) + whole DAG generated on `device`. */
 int nx_epoch_create(int epoch, int device, nx_epoch** out);
 
+/* Same, but with the light cache (nx_light_cache_num_items(epoch) x 64 bytes) supplied by the caller, who ran
+ * the serial chain once for several devices; only the DAG kernel runs. */
+int nx_epoch_create_from_light(int epoch, int device, const uint8_t* light_cache, nx_epoch** out);
+
 /* Multi-GPU build: this rank generates only DAG items [rank*share, min(M,(rank+1)*share)) with
  * share = ceil(M/world), written at their final offset inside a buffer padded to world*share items.
  * The caller then all-gathers nx_epoch_dag_ptr() in place (sendcount = nx_epoch_dag_share_bytes(),
@@ -242,6 +246,32 @@ void nx_sha256d(const uint8_t* data, size_t size, uint8_t out[32]);
 int nx_compact_to_boundary(uint32_t bits, uint8_t out[32]);
 /* CheckProofOfWork (pow.cpp:182-199) on a final hash in progpow byte order: 1 = passes. */
 int nx_check_proof_of_work(const uint8_t final_hash[32], uint32_t bits, const uint8_t pow_limit_be[32]);
+
+/* ------------------------------------------------------------------------------------------------
+ * Miner: one process, all GPUs.  Replaces the nonce loops of miner.cpp:656-713 (CloreMiner) and
+ * rpc/mining.cpp:117-173 (generateBlocks), and the epoch-context handling of hash.cpp:260-266 /
+ * crypto/ethash/lib/ethash/managed.cpp.  Nonce super-batches are dealt round-robin to the devices; the
+ * result is the LOWEST qualifying nonce of the range (host-side min reduction, progpow.cpp:572-577). */
+typedef struct nx_miner nx_miner;
+int nx_miner_create(const int* devices, int n_devices, nx_miner** out); /* devices NULL / n 0 = all visible GPUs */
+void nx_miner_destroy(nx_miner* m);
+int nx_miner_device_count(const nx_miner* m);
+int nx_miner_set_batch(nx_miner* m, uint64_t nonces_per_batch);          /* default 2^22 */
+int nx_miner_set_epoch(nx_miner* m, int epoch);   /* light cache once on the host, one DAG per device, in parallel */
+/* Background: compile the next period's program; prebuild the next epoch when it starts within
+ * lookahead_blocks.  Returns immediately; nx_miner_wait_prepared() joins and reports the outcome. */
+int nx_miner_prepare_async(nx_miner* m, int block_number, int lookahead_blocks);
+int nx_miner_wait_prepared(nx_miner* m);
+int nx_miner_epoch(const nx_miner* m);
+int nx_miner_prepared_epoch(const nx_miner* m);
+const nx_epoch* nx_miner_context(const nx_miner* m, int index);          /* borrowed: the index-th device's context */
+int nx_miner_search(nx_miner* m, int block_number, const uint8_t header_hash[32], const uint8_t boundary[32],
+                    uint64_t start_nonce, uint64_t iterations, const volatile int* cancel, nx_search_result* out);
+int nx_miner_last_stats(const nx_miner* m, uint64_t* hashes, double* seconds);
+/* Header fields in, nBits decoded, nNonce64 scanned: the body of miner.cpp:656-690 in one call. */
+int nx_miner_mine_header(nx_miner* m, int32_t version, const uint8_t prev_block[32], const uint8_t merkle_root[32],
+                         uint32_t time, uint32_t bits, uint32_t height, uint64_t start_nonce, uint64_t max_tries,
+                         const volatile int* cancel, nx_search_result* out);
 
 #ifdef __cplusplus
 }

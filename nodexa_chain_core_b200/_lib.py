@@ -60,6 +60,7 @@ def _load() -> C.CDLL:
         "nx_keccak256": (None, [u8p, sz, u8p]),
         "nx_keccak512": (None, [u8p, sz, u8p]),
         "nx_epoch_create": (i, [i, i, C.POINTER(vp)]),
+        "nx_epoch_create_from_light": (i, [i, i, vp, C.POINTER(vp)]),
         "nx_epoch_create_sharded": (i, [i, i, i, i, C.POINTER(vp)]),
         "nx_epoch_finalize": (i, [vp]),
         "nx_epoch_destroy": (None, [vp]),
@@ -97,6 +98,20 @@ def _load() -> C.CDLL:
         "nx_sha256d": (None, [u8p, sz, u8p]),
         "nx_compact_to_boundary": (i, [u32, u8p]),
         "nx_check_proof_of_work": (i, [u8p, u32, u8p]),
+        "nx_miner_create": (i, [C.POINTER(i), i, C.POINTER(vp)]),
+        "nx_miner_destroy": (None, [vp]),
+        "nx_miner_device_count": (i, [vp]),
+        "nx_miner_set_batch": (i, [vp, u64]),
+        "nx_miner_set_epoch": (i, [vp, i]),
+        "nx_miner_prepare_async": (i, [vp, i, i]),
+        "nx_miner_wait_prepared": (i, [vp]),
+        "nx_miner_epoch": (i, [vp]),
+        "nx_miner_prepared_epoch": (i, [vp]),
+        "nx_miner_context": (vp, [vp, i]),
+        "nx_miner_search": (i, [vp, i, u8p, u8p, u64, u64, C.POINTER(i), C.POINTER(NxSearchResult)]),
+        "nx_miner_last_stats": (i, [vp, C.POINTER(u64), C.POINTER(C.c_double)]),
+        "nx_miner_mine_header": (i, [vp, C.c_int32, u8p, u8p, u32, u32, u32, u64, u64, C.POINTER(i),
+                                     C.POINTER(NxSearchResult)]),
         # introspection (nx_tools.cpp; not part of the drop-in surface)
         "nx_kawpow_program_source": (sz, [u64, u32, i, C.c_char_p, sz]),
         "nx_kawpow_program_ops": (i, [u64, C.POINTER(u32 * 6), i]),

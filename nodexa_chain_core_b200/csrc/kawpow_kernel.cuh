@@ -156,7 +156,7 @@ static const u32 NX_RC800[22] = {
     0x00008002u, 0x00000080u, 0x0000800Au, 0x8000000Au, 0x80008081u, 0x00008080u};
 
 #define NX_CHI(a, b, c) ((a) ^ (~(b) & (c)))
-NX_DEV void nx_keccakf800(u32 a[25])
+NX_DEV void nxk_f800(u32 a[25])
 {
 #ifdef __CUDACC__
 #pragma unroll 1
@@ -299,7 +299,7 @@ NX_DEV void nx_kawpow_body(const uint4* __restrict__ dag, const NxJob& job, u32*
         st[8] = (u32)nonce;
         st[9] = (u32)(nonce >> 32);
         NX_PAD_FIRST(st);
-        nx_keccakf800(st);
+        nxk_f800(st);
         seed0 = st[0];
         seed1 = st[1];
 #pragma unroll
@@ -345,7 +345,7 @@ NX_DEV void nx_kawpow_body(const uint4* __restrict__ dag, const NxJob& job, u32*
 #pragma unroll
     for (int i = 0; i < 8; ++i) st[8 + i] = digest_s[i][tid];
     NX_PAD_LAST(st);
-    nx_keccakf800(st);
+    nxk_f800(st);
 
     if (gid >= job.count) return;
     if (MODE == 0) {

@@ -90,7 +90,7 @@ void destroy(nx_epoch* c)
     delete c;
 }
 
-int create(int epoch, int device, int rank, int world, nx_epoch** out)
+int create(int epoch, int device, int rank, int world, const uint8_t* light_in, nx_epoch** out)
 {
     clear_error();
     if (!out) {
@@ -156,7 +156,10 @@ int create(int epoch, int device, int rank, int world, nx_epoch** out)
     nx_epoch_seed(epoch, seed);
     const char* mode = std::getenv("NX_LIGHT_CACHE");
     const auto t0 = std::chrono::steady_clock::now();
-    if (mode && std::strcmp(mode, "gpu") == 0) {
+    if (light_in) {  // caller already ran the serial chain (one host build shared by several devices)
+        std::memcpy(c->light_host, light_in, light_bytes);
+        NX_TRY(cudaMemcpyAsync(c->light_dev, c->light_host, light_bytes, cudaMemcpyHostToDevice, c->stream));
+    } else if (mode && std::strcmp(mode, "gpu") == 0) {
         int rc = light_cache_build_gpu(c->light_dev, c->light_items, seed, c->stream);
         if (rc != NX_OK) return fail(rc);
         NX_TRY(cudaMemcpyAsync(c->light_host, c->light_dev, light_bytes, cudaMemcpyDeviceToHost, c->stream));
@@ -205,11 +208,20 @@ int nx_device_count(void)
     return n;
 }
 
-int nx_epoch_create(int epoch, int device, nx_epoch** out) { return create(epoch, device, 0, 1, out); }
+int nx_epoch_create(int epoch, int device, nx_epoch** out) { return create(epoch, device, 0, 1, nullptr, out); }
+
+int nx_epoch_create_from_light(int epoch, int device, const uint8_t* light_cache, nx_epoch** out)
+{
+    if (!light_cache) {
+        set_error("null light cache");
+        return NX_ERR_INVALID;
+    }
+    return create(epoch, device, 0, 1, light_cache, out);
+}
 
 int nx_epoch_create_sharded(int epoch, int device, int rank, int world, nx_epoch** out)
 {
-    return create(epoch, device, rank, world, out);
+    return create(epoch, device, rank, world, nullptr, out);
 }
 
 int nx_epoch_finalize(nx_epoch* c)

@@ -89,7 +89,7 @@ kawpow_interp_kernel(const uint4* __restrict__ dag, FastMod32 fm, const KawpowRe
     st[8] = (u32)rec.nonce;
     st[9] = (u32)(rec.nonce >> 32);
     NX_PAD_FIRST(st);
-    nx_keccakf800(st);
+    nxk_f800(st);
     u32 carry[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) carry[i] = st[i];
@@ -142,7 +142,7 @@ kawpow_interp_kernel(const uint4* __restrict__ dag, FastMod32 fm, const KawpowRe
 #pragma unroll
     for (int i = 0; i < 8; ++i) st[8 + i] = dg[i];
     NX_PAD_LAST(st);
-    nx_keccakf800(st);
+    nxk_f800(st);
     if (live && lane == 0) {
         uint4* o = reinterpret_cast<uint4*>(out + (size_t)rec_idx * 16u);
         o[0] = make_uint4(st[0], st[1], st[2], st[3]);

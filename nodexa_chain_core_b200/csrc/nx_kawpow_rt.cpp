@@ -69,11 +69,12 @@ const char* cu_err(CUresult_ r)
     return s ? s : "unknown driver error";
 }
 
-// Kernel shape.  Defaults are the measured best on B200; NX_KAWPOW_TUNE overrides them,
-// e.g. NX_KAWPOW_TUNE="copies=8,threads=1024,minblocks=1,rotimad=1".  Read once per process.
+// Kernel shape.  Defaults are the measured best on B200 (profiles/r1_kawpow_tune_sweep3_sustained.txt: 8 L1
+// replicas in one 1024-thread CTA per SM, 192.2 MH/s sustained vs 186.3 for 1 replica x 4 CTAs of 256);
+// NX_KAWPOW_TUNE overrides them, e.g. NX_KAWPOW_TUNE="copies=1,threads=256,minblocks=4".  Read once per process.
 struct Tune
 {
-    int copies = 1, threads = 256, minblocks = 4, rotimad = 0, l1hi = 0, unroll = 1;
+    int copies = 8, threads = 1024, minblocks = 1, rotimad = 0, l1hi = 0, unroll = 1;
     size_t smem_bytes() const { return (size_t)copies * 16384 + (size_t)14 * 4 * threads; }
     std::string tag() const
     {

@@ -16,7 +16,7 @@ extern "C" void emul_kawpow_hash(const void* oracle_ctx, const uint32_t* l1, con
     st[8] = (u32)nonce;
     st[9] = (u32)(nonce >> 32);
     NX_PAD_FIRST(st);
-    nx_keccakf800(st);
+    nxk_f800(st);
     u32 carry[8];
     memcpy(carry, st, 32);
 
@@ -40,7 +40,7 @@ extern "C" void emul_kawpow_hash(const void* oracle_ctx, const uint32_t* l1, con
     memcpy(st, carry, 32);
     memcpy(st + 8, dg, 32);
     NX_PAD_LAST(st);
-    nx_keccakf800(st);
+    nxk_f800(st);
     memcpy(final_out, st, 32);
     memcpy(mix_out, dg, 32);
 }

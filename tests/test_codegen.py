@@ -81,7 +81,7 @@ def test_generated_program_on_cpu_vs_oracle(nx, oracle, tmp_path, height):
 
 def test_nvrtc_compiles_for_sm100a_without_spills(nx, tmp_path):
     """NVRTC needs no device: the period program must build for sm_100a, stay within 64 registers
-    (4 CTAs x 256 threads per SM) and not spill."""
+    (1024 threads per SM) and not spill."""
     buf = C.create_string_buffer(8 << 20)
     n = nx.lib.nx_kawpow_compile_cubin(1120000, 18874358, buf, len(buf))
     assert n > 0, nx.lib.nx_last_error()
@@ -98,4 +98,4 @@ def test_nvrtc_compiles_for_sm100a_without_spills(nx, tmp_path):
     for name, reg, stack, shared, local in usage:
         assert int(reg) <= 64, (name, reg)
         assert int(stack) == 0 and int(local) == 0, (name, stack, local)
-        assert int(shared) <= 48 * 1024
+        assert int(shared) <= 48 * 1024  # static part only; the L1 replicas are dynamic shared memory

@@ -16,7 +16,7 @@ TUNES = sys.argv[1:] or [
 ]
 for t in TUNES:
     env = dict(os.environ, NX_KAWPOW_TUNE=t)
-    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "10", "--warmup", "3",
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", os.environ.get("SWEEP_STEPS", "10"), "--warmup", "3",
                           "--no-cpu-baseline"], env=env, capture_output=True, text=True, cwd=ROOT)
     try:
         j = json.loads(out.stdout.strip().splitlines()[-1])
