@@ -230,7 +230,7 @@ int nx_epoch_finalize(nx_epoch* c)
         set_error("null epoch context");
         return NX_ERR_INVALID;
     }
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     // KawPow addresses floor(n/2) 256-byte items; classic Ethash also reaches the odd last 128-byte item
     // n-1, i.e. the first half of 256-byte item floor(n/2): generate that one item behind the rest.
@@ -275,7 +275,7 @@ int nx_dag_generate_range(const nx_epoch* cc, uint32_t first, uint32_t count, vo
         set_error("item range [%u,+%u) beyond the DAG (%u items)", first, count, c->dag_items);
         return NX_ERR_INVALID;
     }
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     NX_CUDA(cudaEventRecord(c->ev0, c->stream));
     int rc = dag_generate(c->light_dev, c->light_items, first, count, out_device, c->stream);
@@ -310,7 +310,7 @@ int nx_dag_checksum(const nx_epoch* cc, uint64_t* out)
         set_error("null argument");
         return NX_ERR_INVALID;
     }
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     int rc = dag_checksum(c->dag_dev, (size_t)c->dag_items * 32, c->checksum_partials_dev, CHECKSUM_PARTIALS,
                           c->found_min_dev + 1, c->stream);
@@ -342,7 +342,7 @@ int nx_kawpow_hash_batch_device(const nx_epoch* cc, int block_number, const uint
     if (count == 0) return NX_OK;
     std::shared_ptr<KawpowProgram> p;
     if ((rc = program_for(c, block_number, &p)) != NX_OK) return rc;
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     KawpowJob job;
     fill_job(job, header_hash, nullptr, start_nonce, count, 0);
@@ -368,7 +368,7 @@ int nx_kawpow_hash_batch(const nx_epoch* cc, int block_number, const uint8_t hea
     if (count == 0) return NX_OK;
     std::shared_ptr<KawpowProgram> p;
     if ((rc = program_for(c, block_number, &p)) != NX_OK) return rc;
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     constexpr uint64_t CHUNK = 1ull << 22;  // 256 MiB of results per launch
     if ((rc = ensure_batch_out(c, (size_t)(count < CHUNK ? count : CHUNK) * 64)) != NX_OK) return rc;
@@ -436,7 +436,7 @@ int nx_ethash_hash_batch(const nx_epoch* cc, const uint8_t header_hash[32], uint
         return NX_ERR_INVALID;
     }
     if (count == 0) return NX_OK;
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     constexpr uint64_t CHUNK = 1ull << 22;
     if ((rc = ensure_batch_out(c, (size_t)(count < CHUNK ? count : CHUNK) * 64)) != NX_OK) return rc;
@@ -488,7 +488,7 @@ int nx_kawpow_search_enqueue(const nx_epoch* cc, int block_number, const uint8_t
     if (count == 0) return NX_OK;
     std::shared_ptr<KawpowProgram> p;
     if ((rc = program_for(c, block_number, &p)) != NX_OK) return rc;
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     if (!c->pending) {
         c->found_min_host[0] = NOT_FOUND;
@@ -523,7 +523,7 @@ int nx_kawpow_search_sync(const nx_epoch* cc, nx_search_result* out)
     int block = 0;
     uint8_t header[32];
     {
-        std::lock_guard<std::mutex> lk(c->mu);
+        std::lock_guard<std::recursive_mutex> lk(c->mu);
         if (!c->pending) return NX_OK;
         NX_CUDA(cudaSetDevice(c->device));
         NX_CUDA(cudaEventRecord(c->ev1, c->stream));
@@ -571,7 +571,9 @@ int nx_kawpow_search(const nx_epoch* c, int block_number, const uint8_t header_h
     int rc = check_ctx(c, block_number);
     if (rc != NX_OK) return rc;
     // ascending batches; the first batch with a hit holds the lowest qualifying nonce
-    // (reference progpow.cpp:572-577 returns the first hit of an ascending scan)
+    // (reference progpow.cpp:572-577 returns the first hit of an ascending scan).  The context is held for the
+    // whole scan so that concurrent searches from other host threads cannot interleave their batches with ours.
+    std::lock_guard<std::recursive_mutex> hold(const_cast<nx_epoch*>(c)->mu);
     float total_ms = 0;
     int launches = 0;
     for (uint64_t done = 0; done < iterations; done += SEARCH_BATCH) {
@@ -641,7 +643,7 @@ int nx_kawpow_hash_many(const nx_epoch* cc, const nx_hash_record* records, size_
     std::vector<uint32_t> progs(slot_of.size() * 36 * 4);
     for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);
 
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     const size_t rec_bytes = (n * sizeof(KawpowRecord) + 255) & ~(size_t)255;
     const size_t prog_bytes = (progs.size() * 4 + 255) & ~(size_t)255;

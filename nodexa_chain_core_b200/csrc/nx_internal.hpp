@@ -116,5 +116,6 @@ struct nx_epoch
     float last_kernel_ms = 0.f;
     int last_launches = 0;
     double light_ms = 0, dag_ms = 0;
-    std::mutex mu;  // serialises use of the stream + scratch
+    std::recursive_mutex mu;  // serialises use of the stream + scratch; recursive so that a whole search
+                              // (enqueue, sync, re-hash of the hit) is one critical section
 };

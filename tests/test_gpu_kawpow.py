@@ -168,3 +168,35 @@ def test_search_enqueue_sync_pipelining(ctx_of):
     ms, launches = ctx.last_timing()
     assert launches >= 3 and ms > 0
     assert progpow.search_sync(ctx) == progpow.SearchResult()  # nothing pending
+
+
+def test_concurrent_host_threads_share_one_context(ctx_of):
+    """hash / search / verify are re-entrant on a shared context (SURVEY.md §8b threading): several host
+    threads hammer one context at once (ctypes releases the GIL) and every answer must still be right."""
+    import threading
+    ctx = ctx_of(0)
+    boundary = ((1 << (256 - 13)) - 1).to_bytes(32, "big")
+    jobs = []
+    for t in range(6):
+        hd = hashlib.sha256(b"thread%d" % t).digest()
+        jobs.append((hd, progpow.hash_batch(ctx, 30 + t, hd, t << 20, 2000), progpow.search(ctx, 30 + t, hd, boundary, t << 20, 50000)))
+    errors = []
+
+    def work(t):
+        hd, want_hashes, want_search = jobs[t]
+        try:
+            for _ in range(3):
+                assert progpow.hash_batch(ctx, 30 + t, hd, t << 20, 2000) == want_hashes
+                assert progpow.search(ctx, 30 + t, hd, boundary, t << 20, 50000) == want_search
+                r = progpow.hash(ctx, 30 + t, hd, (t << 20) + 7)
+                assert r.final_hash + r.mix_hash == want_hashes[7 * 64:8 * 64]
+                assert progpow.verify(ctx, 30 + t, hd, r.mix_hash, (t << 20) + 7, r.final_hash)
+        except Exception as e:  # noqa: BLE001
+            errors.append((t, repr(e)))
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(6)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    assert not errors, errors
