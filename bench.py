@@ -100,6 +100,42 @@ def cpu_reference_rate(target_s: float, threads: int):
     return impl.kind, sample, sample / dt / 1e6, dt, ctx_s
 
 
+def cpu_reference_rate_full_dag(ctx, target_s: float, threads: int):
+    """The reference's BEST-CASE CPU path: progpow::hash on an epoch_context_full (progpow.cpp:357-429) whose
+    dataset was pre-filled with the (already verified) GPU-built DAG, so no lazy item generation is timed
+    (BASELINE.md §4 item 4).  Needs oracle/_ref and ~4.5 GiB of host memory; returns None otherwise."""
+    import ctypes as C
+
+    from nodexa_chain_core_b200._lib import check, lib
+    from oracle.oracle import Ref
+    if not Ref.available():
+        return None
+    ref = Ref()
+    try:
+        full = ref.full_ctx_create(EPOCH)
+    except MemoryError:
+        return None
+    try:
+        check(lib.nx_dag_read_items(ctx._h, 0, ctx.dag_num_items, C.cast(ref.full_ctx_dataset_ptr(full), C.POINTER(C.c_uint8))))
+        hd = ref.keccak256(struct.pack("<Q", 1))
+        probe = threads * 64
+        got = ref.kawpow_hash_range_full(full, HEIGHT, hd, 1 << 32, probe, threads)
+        import nodexa_chain_core_b200.progpow as pp
+        assert got == pp.hash_batch(ctx, HEIGHT, hd, 1 << 32, probe), "CPU full-DAG path disagrees with the GPU"
+        t0 = time.perf_counter()
+        ref.kawpow_hash_range_full(full, HEIGHT, hd, (1 << 32) + probe, probe * 4, threads, want_output=False)
+        rate = probe * 4 / (time.perf_counter() - t0)
+        sample = max(probe, int(rate * target_s) // threads * threads)
+        t0 = time.perf_counter()
+        ref.kawpow_hash_range_full(full, HEIGHT, hd, 1 << 33, sample, threads, want_output=False)
+        dt = time.perf_counter() - t0
+        return {"value": sample / dt / 1e6, "unit": "MH/s", "cores": threads, "kind": "reference",
+                "sample": f"{sample} nonces, reference progpow::hash(epoch_context_full) with the dataset pre-filled from the "
+                          f"GPU-built DAG (warm, no lazy generation), {dt:.1f} s; first {probe} results compared with the GPU"}
+    finally:
+        ref.full_ctx_destroy(full)
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -138,6 +174,7 @@ def main():
     ap.add_argument("--epoch", type=int, default=EPOCH)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-full-dag-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
 
@@ -283,6 +320,13 @@ def main():
             line["cpu_baseline"] = {"value": cpu_mhs, "unit": "MH/s", "cores": cores, "kind": kind,
                                     "sample": f"{sample} nonces of the same workload, light context "
                                               f"(progpow::hash), {dt:.1f} s; context build {ctx_s:.1f} s excluded"}
+            if epoch == EPOCH and not args.no_full_dag_baseline:
+                try:
+                    full = cpu_reference_rate_full_dag(ctx, 10.0, cores)
+                    if full:
+                        line["cpu_baseline_full_dag"] = full
+                except Exception as e:  # noqa: BLE001 - a baseline extra must never sink the bench line
+                    line["cpu_baseline_full_dag"] = {"error": repr(e)[:200]}
         print(json.dumps(line), flush=True)
     ctx.close()
     if dist is not None:

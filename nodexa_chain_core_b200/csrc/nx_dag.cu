@@ -237,15 +237,18 @@ __global__ void light_cache_kernel(uint64_t* __restrict__ cache, uint32_t n, uin
 // ---- classic Ethash hash (K7) ----
 // Replaces hash_seed / hash_kernel / hash_final (reference ethash.cpp:257-303) applied to a batch of
 // nonces.  The DAG is addressed as 128-byte items here (index_limit = full_dataset_num_items, :279).
-// No node caller exists for this function; one thread per nonce keeps it simple:
-// 64 dependent 128-byte reads = 8 192 B of DAG per hash.
+// Every thread owns one nonce for the two Keccak calls; the 64-access FNV walk of each nonce is done by its
+// group of 8 lanes together, one nonce after the other: lane s holds mix words 4s..4s+3, so an access is one
+// 16-byte load per lane = one contiguous 128-byte item per group (4 items per warp-wide load).
+// Algorithmic bytes: 64 x 128 B = 8 192 B of DAG per hash.
 constexpr int ETHASH_THREADS = 128;
 __global__ void __launch_bounds__(ETHASH_THREADS)
-ethash_hash_kernel(const uint4* __restrict__ dag, uint32_t num_items_128, uint64_t h0, uint64_t h1, uint64_t h2,
-                   uint64_t h3, uint64_t start_nonce, uint64_t count, uint4* __restrict__ out)
+ethash_hash_kernel(const uint4* __restrict__ dag, FastMod fm, uint64_t h0, uint64_t h1, uint64_t h2, uint64_t h3,
+                   uint64_t start_nonce, uint64_t count, uint4* __restrict__ out)
 {
     const uint64_t gid = (uint64_t)blockIdx.x * ETHASH_THREADS + threadIdx.x;
-    if (gid >= count) return;
+    const uint32_t sub = threadIdx.x & 7u;
+    const bool live = gid < count;  // dead lanes still take part in the shuffles
     uint64_t a[25];
     a[0] = h0; a[1] = h1; a[2] = h2; a[3] = h3;
     a[4] = start_nonce + gid;
@@ -254,33 +257,54 @@ ethash_hash_kernel(const uint4* __restrict__ dag, uint32_t num_items_128, uint64
     for (int i = 6; i < 25; ++i) a[i] = 0;
     a[8] = 0x8000000000000000ULL;  // rate 72 bytes
     keccakf1600(a);
-    uint32_t seed[16], mix[32];
+    uint32_t seed[16];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         seed[2 * i] = (uint32_t)a[i];
         seed[2 * i + 1] = (uint32_t)(a[i] >> 32);
     }
-#pragma unroll
-    for (int i = 0; i < 32; ++i) mix[i] = seed[i & 15];
-#pragma unroll 1
-    for (uint32_t i = 0; i < 64; i += 32) {
-#pragma unroll
-        for (uint32_t ii = 0; ii < 32; ++ii) {
-            const uint32_t p = fnv1((i + ii) ^ seed[0], mix[ii]) % num_items_128;
-            const uint4* src = dag + (size_t)p * 8;
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const uint4 v = __ldg(src + q);
-                mix[4 * q] = fnv1(mix[4 * q], v.x);
-                mix[4 * q + 1] = fnv1(mix[4 * q + 1], v.y);
-                mix[4 * q + 2] = fnv1(mix[4 * q + 2], v.z);
-                mix[4 * q + 3] = fnv1(mix[4 * q + 3], v.w);
-            }
-        }
-    }
     uint32_t mh[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) mh[i] = fnv1(fnv1(fnv1(mix[4 * i], mix[4 * i + 1]), mix[4 * i + 2]), mix[4 * i + 3]);
+    for (int i = 0; i < 8; ++i) mh[i] = 0;
+
+#pragma unroll 1
+    for (uint32_t p = 0; p < 8; ++p) {
+        // the 32-word mix of lane p's nonce starts as its seed twice over: lane s takes words 4s..4s+3,
+        // i.e. seed words (4s+c) mod 16 = 4*(s&3)+c
+        uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+#pragma unroll
+        for (int w = 0; w < 16; ++w) {
+            const uint32_t v = __shfl_sync(0xffffffffu, seed[w], p, 8);
+            if ((uint32_t)(w >> 2) == (sub & 3u)) {
+                if ((w & 3) == 0) m0 = v;
+                if ((w & 3) == 1) m1 = v;
+                if ((w & 3) == 2) m2 = v;
+                if ((w & 3) == 3) m3 = v;
+            }
+        }
+        const uint32_t seed0 = __shfl_sync(0xffffffffu, seed[0], p, 8);
+#pragma unroll 1
+        for (uint32_t i = 0; i < 64; i += 32) {
+#pragma unroll
+            for (uint32_t ii = 0; ii < 32; ++ii) {
+                // mix word ii lives in lane ii/4, component ii%4
+                const uint32_t mine = (ii & 3) == 0 ? m0 : (ii & 3) == 1 ? m1 : (ii & 3) == 2 ? m2 : m3;
+                const uint32_t t = fnv1((i + ii) ^ seed0, __shfl_sync(0xffffffffu, mine, ii >> 2, 8));
+                const uint4 v = __ldg(dag + (size_t)fast_mod(t, fm) * 8 + sub);
+                m0 = fnv1(m0, v.x);
+                m1 = fnv1(m1, v.y);
+                m2 = fnv1(m2, v.z);
+                m3 = fnv1(m3, v.w);
+            }
+        }
+        // lane s now holds words 4s..4s+3 -> compressed word s of the mix hash; hand all 8 to lane p
+        const uint32_t h = fnv1(fnv1(fnv1(m0, m1), m2), m3);
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            const uint32_t v = __shfl_sync(0xffffffffu, h, w, 8);
+            if (sub == p) mh[w] = v;
+        }
+    }
     // final = keccak256(seed[64] || mix_hash[32]): 96 bytes, rate 136
 #pragma unroll
     for (int i = 0; i < 8; ++i) a[i] = (uint64_t)seed[2 * i] | ((uint64_t)seed[2 * i + 1] << 32);
@@ -291,6 +315,7 @@ ethash_hash_kernel(const uint4* __restrict__ dag, uint32_t num_items_128, uint64
     for (int i = 13; i < 25; ++i) a[i] = 0;
     a[16] = 0x8000000000000000ULL;
     keccakf1600(a);
+    if (!live) return;
     uint4* o = out + gid * 4;
     o[0] = make_uint4((uint32_t)a[0], (uint32_t)(a[0] >> 32), (uint32_t)a[1], (uint32_t)(a[1] >> 32));
     o[1] = make_uint4((uint32_t)a[2], (uint32_t)(a[2] >> 32), (uint32_t)a[3], (uint32_t)(a[3] >> 32));
@@ -433,9 +458,11 @@ int ethash_hash_batch(const void* dag_dev, uint32_t num_items_128, const uint8_t
         set_error("ethash batch too large");
         return NX_ERR_INVALID;
     }
-    ethash_hash_kernel<<<(unsigned)blocks, ETHASH_THREADS, 0, s>>>(static_cast<const uint4*>(dag_dev), num_items_128, h[0],
-                                                                  h[1], h[2], h[3], start_nonce, count,
-                                                                  static_cast<uint4*>(out_dev));
+    FastMod fm;
+    fm.d = num_items_128;
+    fm.m = (uint32_t)((1ull << 32) / fm.d);
+    ethash_hash_kernel<<<(unsigned)blocks, ETHASH_THREADS, 0, s>>>(static_cast<const uint4*>(dag_dev), fm, h[0], h[1], h[2],
+                                                                  h[3], start_nonce, count, static_cast<uint4*>(out_dev));
     NX_CUDA(cudaGetLastError());
     return NX_OK;
 }

@@ -238,6 +238,12 @@ class Ref:
         L.nxref_kawpow_hash_no_verify.argtypes = [C.c_int, u8p, u8p, C.c_uint64, u8p]
         L.nxref_kawpow_search_light.argtypes = [vp, C.c_int, u8p, u8p, C.c_uint64, C.c_uint64,
                                                 C.POINTER(C.c_uint64), u8p, u8p]
+        L.nxref_ctx_create_full.restype = vp
+        L.nxref_ctx_create_full.argtypes = [C.c_int]
+        L.nxref_ctx_destroy_full.argtypes = [vp]
+        L.nxref_ctx_full_dataset.restype = vp
+        L.nxref_ctx_full_dataset.argtypes = [vp]
+        L.nxref_kawpow_hash_range_full.argtypes = [vp, C.c_int, u8p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int]
         L.nxref_dataset_item_512.argtypes = [vp, C.c_int64, u8p]
         L.nxref_dataset_item_2048.argtypes = [vp, C.c_uint32, u8p]
         L.nxref_dataset_items_2048.argtypes = [vp, C.c_uint32, C.c_uint32, u8p, C.c_int]
@@ -257,6 +263,24 @@ class Ref:
                 raise MemoryError("reference context")
             self._ctx[epoch] = c
         return self._ctx[epoch]
+
+    # -- full-DAG context (reference's best-case CPU path) --
+    def full_ctx_create(self, epoch):
+        c = self.L.nxref_ctx_create_full(epoch)
+        if not c:
+            raise MemoryError("reference full context")
+        return c
+
+    def full_ctx_dataset_ptr(self, c) -> int:
+        return self.L.nxref_ctx_full_dataset(c)
+
+    def full_ctx_destroy(self, c):
+        self.L.nxref_ctx_destroy_full(c)
+
+    def kawpow_hash_range_full(self, c, height, header, start, count, threads: int = 0, want_output=True):
+        out = _buf(64 * count) if want_output else None
+        self.L.nxref_kawpow_hash_range_full(c, height, _in(header), start, count, out, threads or os.cpu_count() or 1)
+        return bytes(out) if want_output else None
 
     def light_items(self, epoch):
         return self.L.nxref_light_cache_num_items(epoch)

@@ -95,6 +95,40 @@ int nxref_kawpow_search_light(const void* c, int height, const uint8_t header[32
     return r.solution_found ? 1 : 0;
 }
 
+// ---- full-DAG context: the reference's best-case CPU path (progpow.cpp:357-429, lazy DAG) ----
+// ethash_create_epoch_context_full callocs the whole dataset (zero = "not computed yet"); the caller may
+// pre-fill it (e.g. with a DAG that was already verified) so that no lazy item generation happens while timing.
+void* nxref_ctx_create_full(int epoch) { return ethash_create_epoch_context_full(epoch); }
+void nxref_ctx_destroy_full(void* c) { ethash_destroy_epoch_context_full(static_cast<epoch_context_full*>(c)); }
+void* nxref_ctx_full_dataset(void* c) { return static_cast<epoch_context_full*>(c)->full_dataset; }
+
+void nxref_kawpow_hash_range_full(const void* c, int height, const uint8_t header[32], uint64_t start, uint64_t count,
+                                  uint8_t* out, int threads)
+{
+    hash256 h;
+    std::memcpy(h.bytes, header, 32);
+    const epoch_context_full& ctx = *static_cast<const epoch_context_full*>(c);
+    if (threads < 1) threads = 1;
+    std::atomic<uint64_t> next{0};
+    auto work = [&] {
+        for (;;) {
+            const uint64_t i0 = next.fetch_add(64);
+            if (i0 >= count) return;
+            for (uint64_t i = i0; i < i0 + 64 && i < count; ++i) {
+                const result r = progpow::hash(ctx, height, h, start + i);
+                if (out) {
+                    std::memcpy(out + 64 * i, r.final_hash.bytes, 32);
+                    std::memcpy(out + 64 * i + 32, r.mix_hash.bytes, 32);
+                }
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; ++t) pool.emplace_back(work);
+    work();
+    for (auto& t : pool) t.join();
+}
+
 void nxref_dataset_item_512(const void* c, int64_t index, uint8_t out[64])
 {
     const hash512 r = calculate_dataset_item_512(*static_cast<const epoch_context*>(c), index);
