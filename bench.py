@@ -174,6 +174,8 @@ def main():
     ap.add_argument("--epoch", type=int, default=EPOCH)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dag-exchange", default="fused", choices=["fused", "nccl"],
+                    help="N>1: how the DAG slices reach every GPU - peer stores inside the generating kernel, or NCCL")
     ap.add_argument("--no-full-dag-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
@@ -202,10 +204,21 @@ def main():
     epoch, height = args.epoch, args.epoch * 7500
     # ---- epoch context: light cache + DAG.  N>1: each rank builds 1/N of the DAG, one in-place all-gather ----
     t0 = time.perf_counter()
-    ctx = nx.EpochContext(epoch, local, rank=rank, world=world)
+    fused = world > 1 and args.dag_exchange == "fused"
+    ctx = nx.EpochContext(epoch, local, rank=rank, world=world, deferred=fused)
     light_ms, dag_ms = ctx.build_times_ms()
     allgather_ms = 0.0
-    if world > 1:
+    if fused:
+        handles = [None] * world
+        dist.all_gather_object(handles, ctx.ipc_handle())
+        torch.cuda.synchronize()
+        dist.barrier()
+        ctx.generate_fused_ipc(handles)  # K3 stores this rank's slice into every rank's DAG buffer over NVLink
+        torch.cuda.synchronize()
+        dist.barrier()
+        ctx.finalize()
+        light_ms, dag_ms = ctx.build_times_ms()
+    elif world > 1:
         dag = ctx.dag_tensor()
         share = ctx.dag_share_bytes
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -300,7 +313,8 @@ def main():
                        "epoch": epoch, "height": height, "dag_bytes": ctx.dag_bytes, "nonces_per_step_per_gpu": B,
                        "boundary": "0 (no hit)", "l2": "inputs larger than L2 (4.5 GiB DAG, random 256 B reads)",
                        "sharding": f"nonce super-batches round-robin over {world} GPU(s); DAG built 1/{world} per GPU"
-                                   + (" + one NCCL all-gather" if world > 1 else ""),
+                                   + ((" with peer stores fused into the DAG kernel" if fused else " + one NCCL all-gather")
+                                      if world > 1 else ""),
                        "dag_checksum": checksum},
             "wall_ms_per_step": wall_ms / args.steps,
             "e2e": {"value": e2e_mhs, "unit": "MH/s", "h2d_bytes_per_step": 64 + 24 + 8, "d2h_bytes_per_step": 8,

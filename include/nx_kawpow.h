@@ -82,6 +82,18 @@ int nx_epoch_create_sharded(int epoch, int device, int rank, int world, nx_epoch
 int nx_epoch_finalize(nx_epoch* ctx);
 void nx_epoch_destroy(nx_epoch* ctx);
 
+/* Fused generate + all-gather over NVLink peer memory (no NCCL): every rank's DAG kernel stores its slice
+ * straight into the DAG buffer of EVERY rank, so the exchange overlaps the generation instead of following it.
+ *   1. nx_epoch_create_deferred(): allocations + light cache (pass light_cache = NULL to build it), no DAG yet;
+ *   2. exchange buffers: ranks in separate processes trade nx_epoch_ipc_handle() blobs (64 bytes each, any
+ *      transport) and call nx_epoch_generate_fused_ipc(); ranks inside one process enable peer access and call
+ *      nx_epoch_generate_fused_peers() with the nx_epoch_dag_ptr() of every rank;
+ *   3. barrier across ranks (every kernel has finished), then nx_epoch_finalize() on each. */
+int nx_epoch_create_deferred(int epoch, int device, int rank, int world, const uint8_t* light_cache, nx_epoch** out);
+int nx_epoch_ipc_handle(const nx_epoch* ctx, uint8_t handle[64]);
+int nx_epoch_generate_fused_ipc(nx_epoch* ctx, const uint8_t* handles_by_rank /* world x 64 bytes */);
+int nx_epoch_generate_fused_peers(nx_epoch* ctx, void* const* peer_dag_ptrs /* world entries */);
+
 /* Public fields of the reference's struct ethash_epoch_context (ethash.h:35-42). */
 int nx_epoch_number(const nx_epoch* ctx);
 int nx_epoch_light_items(const nx_epoch* ctx);

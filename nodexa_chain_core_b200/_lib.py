@@ -63,6 +63,10 @@ def _load() -> C.CDLL:
         "nx_epoch_create_from_light": (i, [i, i, vp, C.POINTER(vp)]),
         "nx_epoch_create_sharded": (i, [i, i, i, i, C.POINTER(vp)]),
         "nx_epoch_finalize": (i, [vp]),
+        "nx_epoch_create_deferred": (i, [i, i, i, i, vp, C.POINTER(vp)]),
+        "nx_epoch_ipc_handle": (i, [vp, u8p]),
+        "nx_epoch_generate_fused_ipc": (i, [vp, u8p]),
+        "nx_epoch_generate_fused_peers": (i, [vp, C.POINTER(vp)]),
         "nx_epoch_destroy": (None, [vp]),
         "nx_epoch_number": (i, [vp]),
         "nx_epoch_light_items": (i, [vp]),

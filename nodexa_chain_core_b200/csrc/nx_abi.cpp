@@ -76,6 +76,7 @@ void destroy(nx_epoch* c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    for (void* p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     if (c->dag_dev) cudaFree(c->dag_dev);
     if (c->light_dev) cudaFree(c->light_dev);
     if (c->found_min_dev) cudaFree(c->found_min_dev);
@@ -90,7 +91,7 @@ void destroy(nx_epoch* c)
     delete c;
 }
 
-int create(int epoch, int device, int rank, int world, const uint8_t* light_in, nx_epoch** out)
+int create(int epoch, int device, int rank, int world, const uint8_t* light_in, bool deferred, nx_epoch** out)
 {
     clear_error();
     if (!out) {
@@ -177,17 +178,20 @@ int create(int epoch, int device, int rank, int world, const uint8_t* light_in, 
     if (c->dag_padded_bytes > (size_t)c->dag_items * 256)  // padding tail is never addressed; keep it defined
         NX_TRY(cudaMemsetAsync((char*)c->dag_dev + (size_t)c->dag_items * 256, 0,
                                c->dag_padded_bytes - (size_t)c->dag_items * 256, c->stream));
-    NX_TRY(cudaEventRecord(c->ev0, c->stream));
-    {
+    c->deferred = deferred;
+    if (!deferred) {
+        NX_TRY(cudaEventRecord(c->ev0, c->stream));
         int rc = dag_generate(c->light_dev, c->light_items, first, count, (char*)c->dag_dev + (size_t)first * 256,
                               c->stream);
         if (rc != NX_OK) return fail(rc);
+        NX_TRY(cudaEventRecord(c->ev1, c->stream));
     }
-    NX_TRY(cudaEventRecord(c->ev1, c->stream));
     NX_TRY(cudaStreamSynchronize(c->stream));
-    float ms = 0;
-    NX_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    c->dag_ms = ms;
+    if (!deferred) {
+        float ms = 0;
+        NX_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        c->dag_ms = ms;
+    }
 #undef NX_TRY
 
     *out = c;
@@ -208,7 +212,7 @@ int nx_device_count(void)
     return n;
 }
 
-int nx_epoch_create(int epoch, int device, nx_epoch** out) { return create(epoch, device, 0, 1, nullptr, out); }
+int nx_epoch_create(int epoch, int device, nx_epoch** out) { return create(epoch, device, 0, 1, nullptr, false, out); }
 
 int nx_epoch_create_from_light(int epoch, int device, const uint8_t* light_cache, nx_epoch** out)
 {
@@ -216,12 +220,98 @@ int nx_epoch_create_from_light(int epoch, int device, const uint8_t* light_cache
         set_error("null light cache");
         return NX_ERR_INVALID;
     }
-    return create(epoch, device, 0, 1, light_cache, out);
+    return create(epoch, device, 0, 1, light_cache, false, out);
 }
 
 int nx_epoch_create_sharded(int epoch, int device, int rank, int world, nx_epoch** out)
 {
-    return create(epoch, device, rank, world, nullptr, out);
+    return create(epoch, device, rank, world, nullptr, false, out);
+}
+
+int nx_epoch_create_deferred(int epoch, int device, int rank, int world, const uint8_t* light_cache, nx_epoch** out)
+{
+    return create(epoch, device, rank, world, light_cache, true, out);
+}
+
+int nx_epoch_ipc_handle(const nx_epoch* c, uint8_t handle[64])
+{
+    if (!c || !handle) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    NX_CUDA(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    NX_CUDA(cudaIpcGetMemHandle(&h, c->dag_dev));
+    std::memcpy(handle, &h, 64);
+    return NX_OK;
+}
+
+// Generate this rank's slice and store it into every rank's DAG buffer in the same kernel.
+static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries; [rank] may be null */)
+{
+    if (!c->deferred) {
+        set_error("context was not created with nx_epoch_create_deferred (its slice is already generated)");
+        return NX_ERR_STATE;
+    }
+    if (c->world > NX_MAX_PEERS) {
+        set_error("world %d exceeds the %d peers one launch can address", c->world, NX_MAX_PEERS);
+        return NX_ERR_INVALID;
+    }
+    const uint32_t first = (uint32_t)c->rank * c->share_items;
+    const uint32_t last = first + c->share_items < c->dag_items ? first + c->share_items : c->dag_items;
+    const uint32_t count = last > first ? last - first : 0;
+    void* outs[NX_MAX_PEERS];
+    int n = 0;
+    outs[n++] = (char*)c->dag_dev + (size_t)first * 256;  // local copy first
+    for (int r = 0; r < c->world; ++r)
+        if (r != c->rank) outs[n++] = (char*)peer_bases[r] + (size_t)first * 256;
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+    const int rc = dag_generate_multi(c->light_dev, c->light_items, first, count, outs, n, c->stream);
+    if (rc != NX_OK) return rc;
+    NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+    NX_CUDA(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    NX_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->dag_ms = ms;
+    c->deferred = false;
+    return NX_OK;
+}
+
+int nx_epoch_generate_fused_ipc(nx_epoch* c, const uint8_t* handles /* world x 64 bytes, indexed by rank */)
+{
+    if (!c || !handles) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    NX_CUDA(cudaSetDevice(c->device));
+    std::vector<void*> bases((size_t)c->world, nullptr);
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank) continue;
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + 64 * (size_t)r, 64);
+        void* p = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            set_error("cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e));
+            cudaGetLastError();
+            return NX_ERR_CUDA;
+        }
+        c->ipc_opened.push_back(p);
+        bases[(size_t)r] = p;
+    }
+    return generate_fused(c, bases.data());
+}
+
+int nx_epoch_generate_fused_peers(nx_epoch* c, void* const* peer_dag_ptrs /* world entries, same process */)
+{
+    if (!c || !peer_dag_ptrs) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    return generate_fused(c, peer_dag_ptrs);
 }
 
 int nx_epoch_finalize(nx_epoch* c)

@@ -83,9 +83,17 @@ __device__ __forceinline__ void quad_gather(const uint32_t a[4][4], uint32_t w[1
 // lanes of a quad for their four items AT THE SAME TIME: lane s holds words 4s..4s+3 of each item, so every
 // step issues four independent 16-byte loads per lane (64 contiguous bytes per parent across the quad).
 // Four parents in flight per lane is what hides the L2 latency of the gather.
+// Fused generate + all-gather: the slice is stored into the DAG buffer of EVERY GPU of the job (outs.ptr[0] is
+// the local one, the others are peer-mapped pointers reached over NVLink), so the exchange overlaps the L2
+// gather instead of following it as a separate collective.
+struct DagOuts
+{
+    uint4* ptr[NX_MAX_PEERS];  // each already offset to the first item of this launch
+    int n;
+};
+
 __global__ void __launch_bounds__(DAG_THREADS)
-dag_items_kernel(const uint4* __restrict__ light, FastMod fm, uint32_t first512, uint32_t count512,
-                 uint4* __restrict__ out)
+dag_items_kernel(const uint4* __restrict__ light, FastMod fm, uint32_t first512, uint32_t count512, DagOuts outs)
 {
     const uint32_t gid = blockIdx.x * DAG_THREADS + threadIdx.x;
     const uint32_t sub = threadIdx.x & 3u;
@@ -146,11 +154,16 @@ dag_items_kernel(const uint4* __restrict__ light, FastMod fm, uint32_t first512,
         keccak512_64(w);
         if (live) {
             // streaming stores: the DAG is written once and must not push the light cache out of L2
-            uint4* dst = out + (size_t)gid * 4;
+            uint4 v[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                __stcs(dst + i, make_uint4((uint32_t)w[2 * i], (uint32_t)(w[2 * i] >> 32), (uint32_t)w[2 * i + 1],
-                                           (uint32_t)(w[2 * i + 1] >> 32)));
+                v[i] = make_uint4((uint32_t)w[2 * i], (uint32_t)(w[2 * i] >> 32), (uint32_t)w[2 * i + 1],
+                                  (uint32_t)(w[2 * i + 1] >> 32));
+            for (int t = 0; t < outs.n; ++t) {
+                uint4* dst = outs.ptr[t] + (size_t)gid * 4;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) __stcs(dst + i, v[i]);
+            }
         }
     }
 }
@@ -431,7 +444,18 @@ namespace nx
 int dag_generate(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256, void* out_dev,
                  cudaStream_t s)
 {
+    void* one[1] = {out_dev};
+    return dag_generate_multi(light_dev, light_items, first_item256, count_item256, one, 1, s);
+}
+
+int dag_generate_multi(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256,
+                       void* const* outs_dev, int n_outs, cudaStream_t s)
+{
     if (count_item256 == 0) return NX_OK;
+    if (n_outs < 1 || n_outs > NX_MAX_PEERS) {
+        set_error("dag_generate: %d output buffers (1..%d supported)", n_outs, NX_MAX_PEERS);
+        return NX_ERR_INVALID;
+    }
     const uint64_t count512 = (uint64_t)count_item256 * 4;
     if ((uint64_t)first_item256 * 4 + count512 > 0xffffffffull) {
         set_error("dag_generate: item range exceeds 32-bit index space");
@@ -441,8 +465,11 @@ int dag_generate(const void* light_dev, int light_items, uint32_t first_item256,
     fm.d = (uint32_t)light_items;
     fm.m = (uint32_t)((1ull << 32) / fm.d);
     const uint32_t blocks = (uint32_t)((count512 + DAG_THREADS - 1) / DAG_THREADS);
+    DagOuts outs;
+    outs.n = n_outs;
+    for (int i = 0; i < NX_MAX_PEERS; ++i) outs.ptr[i] = i < n_outs ? static_cast<uint4*>(outs_dev[i]) : nullptr;
     dag_items_kernel<<<blocks, DAG_THREADS, 0, s>>>(static_cast<const uint4*>(light_dev), fm, first_item256 * 4u,
-                                                    (uint32_t)count512, static_cast<uint4*>(out_dev));
+                                                    (uint32_t)count512, outs);
     NX_CUDA(cudaGetLastError());
     return NX_OK;
 }

@@ -70,8 +70,12 @@ int kawpow_interp_launch(const void* dag, uint32_t dag_items, const KawpowRecord
 bool kawpow_program_is_cached(int device, uint64_t prog_seed, uint32_t dag_items_256);
 
 // ---- CUDA kernels (nx_dag.cu) ----
+constexpr int NX_MAX_PEERS = 16;
 int dag_generate(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256,
                  void* out_dev, cudaStream_t s);
+// same slice stored into n_outs buffers (local + peer-mapped); each pointer already offset to the slice start
+int dag_generate_multi(const void* light_dev, int light_items, uint32_t first_item256, uint32_t count_item256,
+                       void* const* outs_dev, int n_outs, cudaStream_t s);
 int ethash_hash_batch(const void* dag_dev, uint32_t num_items_128, const uint8_t header[32], uint64_t start_nonce,
                       uint64_t count, void* out_dev, cudaStream_t s);
 int light_cache_build_gpu(void* light_dev, int light_items, const uint8_t seed[32], cudaStream_t s);
@@ -105,6 +109,8 @@ struct nx_epoch
     uint64_t* checksum_partials_dev = nullptr;
     void* batch_out_dev = nullptr;
     size_t batch_out_bytes = 0;
+    bool deferred = false;     // slice not generated yet (waiting for nx_epoch_generate_fused*)
+    std::vector<void*> ipc_opened;  // peer DAG buffers opened with cudaIpcOpenMemHandle
     void* many_dev = nullptr;  // records + packed programs of nx_kawpow_hash_many
     size_t many_bytes = 0;
     // bookkeeping for enqueue/sync

@@ -14,6 +14,8 @@
 #include <atomic>
 #include <chrono>
 #include <cstring>
+#include <cstdlib>
+#include <functional>
 #include <future>
 #include <thread>
 
@@ -42,7 +44,38 @@ void destroy_all(std::vector<nx_epoch*>& v)
     v.clear();
 }
 
-// Light cache once on the host, then one DAG per device in parallel.
+// Light cache once on the host.  With peer access between all devices each device then generates 1/N of the
+// DAG and its kernel stores the slice into every device's buffer (fused generate + all-gather over NVLink);
+// otherwise every device generates the whole DAG for itself.  Either way the devices work in parallel.
+bool all_peers_reachable(const std::vector<int>& devices)
+{
+    if (devices.size() < 2 || devices.size() > (size_t)NX_MAX_PEERS) return false;
+    if (const char* e = std::getenv("NX_MINER_NO_P2P"))
+        if (*e && *e != '0') return false;
+    for (int a : devices)
+        for (int b : devices) {
+            if (a == b) continue;
+            int ok = 0;
+            if (cudaDeviceCanAccessPeer(&ok, a, b) != cudaSuccess || !ok) {
+                cudaGetLastError();
+                return false;
+            }
+        }
+    for (int a : devices) {
+        if (cudaSetDevice(a) != cudaSuccess) return false;
+        for (int b : devices) {
+            if (a == b) continue;
+            const cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+                return false;
+            }
+            cudaGetLastError();
+        }
+    }
+    return true;
+}
+
 int build_contexts(const std::vector<int>& devices, int epoch, std::vector<nx_epoch*>& out)
 {
     const int n_light = nx_light_cache_num_items(epoch);
@@ -51,17 +84,31 @@ int build_contexts(const std::vector<int>& devices, int epoch, std::vector<nx_ep
     nx_epoch_seed(epoch, seed);
     host_build_light_cache(light.data(), n_light, seed);
 
-    out.assign(devices.size(), nullptr);
-    std::vector<int> rcs(devices.size(), NX_OK);
-    std::vector<std::string> errs(devices.size());
-    std::vector<std::thread> th;
-    for (size_t i = 0; i < devices.size(); ++i)
-        th.emplace_back([&, i] {
-            rcs[i] = nx_epoch_create_from_light(epoch, devices[i], light.data(), &out[i]);
-            if (rcs[i] != NX_OK) errs[i] = nx_last_error();
-        });
-    for (auto& t : th) t.join();
-    for (size_t i = 0; i < devices.size(); ++i)
+    const size_t n = devices.size();
+    const bool fused = all_peers_reachable(devices);
+    out.assign(n, nullptr);
+    std::vector<int> rcs(n, NX_OK);
+    std::vector<std::string> errs(n);
+    auto run_all = [&](const std::function<int(size_t)>& fn) {
+        std::vector<std::thread> th;
+        for (size_t i = 0; i < n; ++i)
+            th.emplace_back([&, i] {
+                if (rcs[i] != NX_OK) return;
+                rcs[i] = fn(i);
+                if (rcs[i] != NX_OK) errs[i] = nx_last_error();
+            });
+        for (auto& t : th) t.join();  // doubles as the barrier between the phases
+    };
+    if (fused) {
+        run_all([&](size_t i) { return nx_epoch_create_deferred(epoch, devices[i], (int)i, (int)n, light.data(), &out[i]); });
+        std::vector<void*> bases(n, nullptr);
+        for (size_t i = 0; i < n; ++i) bases[i] = out[i] ? nx_epoch_dag_ptr(out[i]) : nullptr;
+        run_all([&](size_t i) { return nx_epoch_generate_fused_peers(out[i], bases.data()); });
+        run_all([&](size_t i) { return nx_epoch_finalize(out[i]); });
+    } else {
+        run_all([&](size_t i) { return nx_epoch_create_from_light(epoch, devices[i], light.data(), &out[i]); });
+    }
+    for (size_t i = 0; i < n; ++i)
         if (rcs[i] != NX_OK) {
             set_error("device %d: %s", devices[i], errs[i].c_str());
             destroy_all(out);

@@ -55,9 +55,11 @@ class EpochContext:
     distinguishes a light and a full context; on B200 both hold the resident DAG.
     """
 
-    def __init__(self, epoch_number: int, device: int = 0, rank: int = 0, world: int = 1):
+    def __init__(self, epoch_number: int, device: int = 0, rank: int = 0, world: int = 1, deferred: bool = False):
         h = C.c_void_p()
-        if world == 1:
+        if deferred:
+            check(lib.nx_epoch_create_deferred(epoch_number, device, rank, world, None, C.byref(h)))
+        elif world == 1:
             check(lib.nx_epoch_create(epoch_number, device, C.byref(h)))
         else:
             check(lib.nx_epoch_create_sharded(epoch_number, device, rank, world, C.byref(h)))
@@ -116,6 +118,16 @@ class EpochContext:
         a, b = C.c_double(), C.c_double()
         lib.nx_epoch_build_times(self._h, C.byref(a), C.byref(b))
         return a.value, b.value
+
+    def ipc_handle(self) -> bytes:
+        o = outb(64)
+        check(lib.nx_epoch_ipc_handle(self._h, o))
+        return bytes(o)
+
+    def generate_fused_ipc(self, handles_by_rank) -> None:
+        """handles_by_rank: list of `world` 64-byte blobs from every rank's ipc_handle() (own entry ignored)."""
+        blob = b"".join(handles_by_rank)
+        check(lib.nx_epoch_generate_fused_ipc(self._h, inb(blob)))
 
     def finalize(self):
         """After the caller's in-place all-gather of a sharded DAG."""

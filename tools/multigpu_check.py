@@ -18,6 +18,7 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--epoch", type=int, default=0)
+    ap.add_argument("--fused", action="store_true", help="DAG exchange inside the generating kernel (peer stores via CUDA IPC) instead of NCCL")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -30,18 +31,29 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     dev = f"cuda:{local}"
 
-    ctx = nx.EpochContext(a.epoch, local, rank=rank, world=world)
-    dag = ctx.dag_tensor()
+    ctx = nx.EpochContext(a.epoch, local, rank=rank, world=world, deferred=a.fused)
     share = ctx.dag_share_bytes
     first, last = sharding.dag_slice(ctx.dag_num_items, rank, world)
     assert share == sharding.dag_share_items(ctx.dag_num_items, world) * 256
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    dist.barrier()
-    e0.record()
-    dist.all_gather_into_tensor(dag, dag[rank * share:(rank + 1) * share])
-    e1.record()
-    torch.cuda.synchronize()
+    if a.fused:
+        handles = [None] * world
+        dist.all_gather_object(handles, ctx.ipc_handle())
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0.record()
+        ctx.generate_fused_ipc(handles)   # one kernel: generate my slice, store it into every rank's DAG
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier()                    # every rank's kernel has finished writing into my buffer
+    else:
+        dag = ctx.dag_tensor()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0.record()
+        dist.all_gather_into_tensor(dag, dag[rank * share:(rank + 1) * share])
+        e1.record()
+        torch.cuda.synchronize()
     ctx.finalize()
     gold = json.load(open(os.path.join(ROOT, "tests", "golden", "dag_digest.json")))[str(a.epoch)]
     cs = ctx.checksum()
@@ -69,7 +81,8 @@ def main():
     t = torch.tensor([dag_ms, e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
-        print(json.dumps({"multigpu_check": "ok", "world": world, "epoch": a.epoch, "dag_kernel_ms_max": t[0].item(),
+        print(json.dumps({"multigpu_check": "ok", "exchange": "fused peer stores (IPC)" if a.fused else "nccl all-gather",
+                          "world": world, "epoch": a.epoch, "dag_kernel_ms_max": t[0].item(),
                           "allgather_ms_max": t[1].item(), "allgather_GBps_per_gpu_recv": share * (world - 1) / t[1].item() / 1e6,
                           "found_nonce": single.nonce}))
     ctx.close()
