@@ -663,6 +663,9 @@ int nx_kawpow_search(const nx_epoch* c, int block_number, const uint8_t header_h
     // ascending batches; the first batch with a hit holds the lowest qualifying nonce
     // (reference progpow.cpp:572-577 returns the first hit of an ascending scan).  The context is held for the
     // whole scan so that concurrent searches from other host threads cannot interleave their batches with ours.
+    // The reference's loop is `for (nonce = start; nonce < start + iterations; ++nonce)` in uint64_t: when the
+    // end wraps past 2^64 it is not above the start and nothing is scanned.  Same here.
+    if (start_nonce + iterations <= start_nonce) return NX_OK;
     std::lock_guard<std::recursive_mutex> hold(const_cast<nx_epoch*>(c)->mu);
     float total_ms = 0;
     int launches = 0;

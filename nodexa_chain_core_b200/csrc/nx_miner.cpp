@@ -277,6 +277,7 @@ int nx_miner_search(nx_miner* m, int block_number, const uint8_t header_hash[32]
     }
     int rc = nx_miner_set_epoch(m, block_number / NX_EPOCH_LENGTH);
     if (rc != NX_OK) return rc;
+    if (start_nonce + iterations <= start_nonce) return NX_OK;  // uint64_t wrap: the reference's loop scans nothing
     std::vector<nx_epoch*> ctxs;
     {
         std::lock_guard<std::mutex> lk(m->mu);

@@ -66,6 +66,8 @@ def search_sharded(ctx, block_number: int, header_hash: bytes, boundary: bytes, 
     """progpow::search over [start_nonce, start_nonce+iterations) split across `world` GPUs.
     Returns the same SearchResult on every rank (lowest qualifying nonce, or the all-zero result)."""
     from . import progpow
+    if (start_nonce + iterations) % 2**64 <= start_nonce:  # uint64_t wrap: the reference's loop scans nothing
+        return progpow.SearchResult()
     plan = ShardedSearchPlan(start_nonce, iterations, batch, world)
     for k in range(plan.rounds):
         s, n = plan.window(k, rank)

@@ -153,6 +153,11 @@ def test_search_returns_lowest_nonce_across_batches(ctx_of):
     below = (int.from_bytes(finals[100], "big") - 1).to_bytes(32, "big")
     assert not progpow.search(ctx, 300, hd, below, start + 100, 1).solution_found
     assert not progpow.search(ctx, 300, hd, boundary, start, 0).solution_found
+    # uint64_t wrap-around: the reference's `nonce < start + iterations` loop does not run when the end wraps
+    easy = b"\xff" * 32
+    assert progpow.search(ctx, 300, hd, easy, 2**64 - 10, 9).nonce == 2**64 - 10
+    assert not progpow.search(ctx, 300, hd, easy, 2**64 - 10, 10).solution_found
+    assert not progpow.search(ctx, 300, hd, easy, 2**64 - 10, 500).solution_found
 
 
 def test_search_enqueue_sync_pipelining(ctx_of):
