@@ -10,7 +10,7 @@ ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function,-Wno-unknown-pragmas -Iinclude -I$(SRC)
 CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp nx_compat.cpp nx_miner.cpp
 CUSRC     := nx_dag.cu nx_kawpow_interp.cu
-OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o))
+OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o)) $(OBJ)/nx_lightcache_avx512.o $(OBJ)/nx_cpu_dispatch.o
 
 .PHONY: all lib oracle ref clean
 all: lib oracle
@@ -22,6 +22,14 @@ $(SRC)/kawpow_kernel_src.inc: $(SRC)/kawpow_kernel.cuh
 
 $(OBJ)/nx_kernel_src.o: $(SRC)/kawpow_kernel_src.inc
 $(OBJ)/nx_kawpow_interp.o: $(SRC)/kawpow_kernel.cuh
+
+# plain host code built by g++ directly: the AVX-512 light-cache chain (only called when the CPU has AVX-512F)
+$(OBJ)/nx_lightcache_avx512.o: $(SRC)/nx_lightcache_avx512.cpp
+	@mkdir -p $(OBJ)
+	g++ -O3 -std=c++17 -fPIC -Wall -mavx512f -c $< -o $@
+$(OBJ)/nx_cpu_dispatch.o: $(SRC)/nx_cpu_dispatch.cpp
+	@mkdir -p $(OBJ)
+	g++ -O2 -std=c++17 -fPIC -Wall -c $< -o $@
 
 $(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/nx_internal.hpp $(SRC)/nx_keccak.cuh include/nx_kawpow.h include/nx/ethash_compat.h include/nx/ethash_compat.hpp
 	@mkdir -p $(OBJ)

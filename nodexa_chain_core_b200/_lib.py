@@ -121,6 +121,8 @@ def _load() -> C.CDLL:
         "nx_kawpow_program_ops": (i, [u64, C.POINTER(u32 * 6), i]),
         "nx_kawpow_compile_cubin": (C.c_long, [u64, u32, C.c_char_p, sz]),
         "nx_host_light_cache": (None, [i, vp]),
+        "nx_host_light_cache_variant": (i, [i, i, vp]),
+        "nx_keccakf1600_avx512": (i, [C.POINTER(u64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

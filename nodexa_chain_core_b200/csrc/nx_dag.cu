@@ -251,7 +251,7 @@ __global__ void light_cache_kernel(uint64_t* __restrict__ cache, uint32_t n, uin
 // Replaces hash_seed / hash_kernel / hash_final (reference ethash.cpp:257-303) applied to a batch of
 // nonces.  The DAG is addressed as 128-byte items here (index_limit = full_dataset_num_items, :279).
 // Every thread owns one nonce for the two Keccak calls; the 64-access FNV walk of each nonce is done by its
-// group of 8 lanes together, one nonce after the other: lane s holds mix words 4s..4s+3, so an access is one
+// group of 8 lanes together, four nonces at a time: lane s holds mix words 4s..4s+3 of each, so an access is one
 // 16-byte load per lane = one contiguous 128-byte item per group (4 items per warp-wide load).
 // Algorithmic bytes: 64 x 128 B = 8 192 B of DAG per hash.
 constexpr int ETHASH_THREADS = 128;
@@ -280,42 +280,53 @@ ethash_hash_kernel(const uint4* __restrict__ dag, FastMod fm, uint64_t h0, uint6
 #pragma unroll
     for (int i = 0; i < 8; ++i) mh[i] = 0;
 
+    // Four nonces of the group are walked at the same time (four independent 128-byte reads in flight per group).
 #pragma unroll 1
-    for (uint32_t p = 0; p < 8; ++p) {
-        // the 32-word mix of lane p's nonce starts as its seed twice over: lane s takes words 4s..4s+3,
+    for (uint32_t p0 = 0; p0 < 8; p0 += 4) {
+        // the 32-word mix of a nonce starts as its seed twice over: lane s takes words 4s..4s+3,
         // i.e. seed words (4s+c) mod 16 = 4*(s&3)+c
-        uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+        uint32_t m[4][4];
+        uint32_t seed0[4];
 #pragma unroll
-        for (int w = 0; w < 16; ++w) {
-            const uint32_t v = __shfl_sync(0xffffffffu, seed[w], p, 8);
-            if ((uint32_t)(w >> 2) == (sub & 3u)) {
-                if ((w & 3) == 0) m0 = v;
-                if ((w & 3) == 1) m1 = v;
-                if ((w & 3) == 2) m2 = v;
-                if ((w & 3) == 3) m3 = v;
+        for (int q = 0; q < 4; ++q) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) m[q][c] = 0;
+#pragma unroll
+            for (int w = 0; w < 16; ++w) {
+                const uint32_t v = __shfl_sync(0xffffffffu, seed[w], p0 + q, 8);
+                if ((uint32_t)(w >> 2) == (sub & 3u)) m[q][w & 3] = v;
             }
+            seed0[q] = __shfl_sync(0xffffffffu, seed[0], p0 + q, 8);
         }
-        const uint32_t seed0 = __shfl_sync(0xffffffffu, seed[0], p, 8);
 #pragma unroll 1
         for (uint32_t i = 0; i < 64; i += 32) {
 #pragma unroll
             for (uint32_t ii = 0; ii < 32; ++ii) {
                 // mix word ii lives in lane ii/4, component ii%4
-                const uint32_t mine = (ii & 3) == 0 ? m0 : (ii & 3) == 1 ? m1 : (ii & 3) == 2 ? m2 : m3;
-                const uint32_t t = fnv1((i + ii) ^ seed0, __shfl_sync(0xffffffffu, mine, ii >> 2, 8));
-                const uint4 v = __ldg(dag + (size_t)fast_mod(t, fm) * 8 + sub);
-                m0 = fnv1(m0, v.x);
-                m1 = fnv1(m1, v.y);
-                m2 = fnv1(m2, v.z);
-                m3 = fnv1(m3, v.w);
+                uint4 v[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t t = fnv1((i + ii) ^ seed0[q], __shfl_sync(0xffffffffu, m[q][ii & 3], ii >> 2, 8));
+                    v[q] = __ldg(dag + (size_t)fast_mod(t, fm) * 8 + sub);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    m[q][0] = fnv1(m[q][0], v[q].x);
+                    m[q][1] = fnv1(m[q][1], v[q].y);
+                    m[q][2] = fnv1(m[q][2], v[q].z);
+                    m[q][3] = fnv1(m[q][3], v[q].w);
+                }
             }
         }
-        // lane s now holds words 4s..4s+3 -> compressed word s of the mix hash; hand all 8 to lane p
-        const uint32_t h = fnv1(fnv1(fnv1(m0, m1), m2), m3);
+        // lane s holds words 4s..4s+3 -> compressed word s of each mix hash; hand all 8 words to the owner lane
 #pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            const uint32_t v = __shfl_sync(0xffffffffu, h, w, 8);
-            if (sub == p) mh[w] = v;
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t h = fnv1(fnv1(fnv1(m[q][0], m[q][1]), m[q][2]), m[q][3]);
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+                const uint32_t v = __shfl_sync(0xffffffffu, h, w, 8);
+                if (sub == p0 + q) mh[w] = v;
+            }
         }
     }
     // final = keccak256(seed[64] || mix_hash[32]): 96 bytes, rate 136

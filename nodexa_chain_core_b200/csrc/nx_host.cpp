@@ -44,8 +44,17 @@ static void sponge(uint8_t* out, size_t outlen, const uint8_t* data, size_t size
     std::memcpy(out, st, outlen);
 }
 
-// reference lib/ethash/ethash.cpp:101-129 — 4*n dependent keccak512 calls; no parallelism to extract.
+// reference lib/ethash/ethash.cpp:101-129 — 4*n dependent keccak512 calls; no parallelism to extract, so the
+// only lever is the latency of one permutation: AVX-512 version where the CPU has it, scalar otherwise.
 void host_build_light_cache(uint8_t* cache, int n, const uint8_t seed[32])
+{
+    if (cpu_has_avx512f())
+        host_build_light_cache_avx512(cache, n, seed);
+    else
+        host_build_light_cache_scalar(cache, n, seed);
+}
+
+void host_build_light_cache_scalar(uint8_t* cache, int n, const uint8_t seed[32])
 {
     uint64_t* c = reinterpret_cast<uint64_t*>(cache);
     uint64_t in[4], item[8];

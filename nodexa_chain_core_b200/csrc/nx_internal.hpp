@@ -27,7 +27,11 @@ void clear_error();
     } while (0)
 
 // ---- host algorithms (nx_host.cpp) ----
-void host_build_light_cache(uint8_t* cache, int num_items, const uint8_t seed[32]);
+void host_build_light_cache(uint8_t* cache, int num_items, const uint8_t seed[32]);  // dispatches on the CPU
+void host_build_light_cache_scalar(uint8_t* cache, int num_items, const uint8_t seed[32]);
+void host_build_light_cache_avx512(uint8_t* cache, int num_items, const uint8_t seed[32]);  // nx_lightcache_avx512.cpp
+void keccakf1600_avx512(uint64_t a[25]);
+bool cpu_has_avx512f();  // nx_cpu_dispatch.cpp
 
 // ---- program generator (nx_codegen.cpp) ----
 struct ProgramOp

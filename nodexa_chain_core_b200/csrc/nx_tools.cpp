@@ -62,3 +62,29 @@ void nx_host_light_cache(int epoch, uint8_t* out)
     host_build_light_cache(out, nx_light_cache_num_items(epoch), seed);
 }
 }
+
+extern "C" {
+// which = 0: dispatching entry, 1: scalar, 2: AVX-512 (returns -1 when the CPU lacks it).  CPU tests time and compare them.
+int nx_host_light_cache_variant(int epoch, int which, uint8_t* out)
+{
+    uint8_t seed[32];
+    nx_epoch_seed(epoch, seed);
+    const int n = nx_light_cache_num_items(epoch);
+    if (which == 2) {
+        if (!cpu_has_avx512f()) return -1;
+        host_build_light_cache_avx512(out, n, seed);
+    } else if (which == 1) {
+        host_build_light_cache_scalar(out, n, seed);
+    } else {
+        host_build_light_cache(out, n, seed);
+    }
+    return 0;
+}
+
+int nx_keccakf1600_avx512(uint64_t state[25])
+{
+    if (!cpu_has_avx512f()) return -1;
+    keccakf1600_avx512(state);
+    return 0;
+}
+}

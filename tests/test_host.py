@@ -98,17 +98,38 @@ def test_check_proof_of_work():
 
 
 def test_host_light_cache_vs_reference_digest():
-    """The product's own (host) light-cache chain for epoch 0 and the mainnet-sized epoch 448."""
+    """The product's own host light-cache chain (scalar and, where the CPU has it, AVX-512) for epoch 0 and the
+    mainnet-sized epoch 448, against the digest of the reference's light cache."""
     import hashlib
     import time
     e = golden("epochs.json")
     for epoch in (0, 448):
         n = ethash.calculate_light_cache_num_items(epoch)
-        buf = C.create_string_buffer(n * 64)
-        t = time.time()
-        lib.nx_host_light_cache(epoch, buf)
-        dt = time.time() - t
-        assert hashlib.sha256(buf.raw).hexdigest() == e[f"light_cache_sha256_epoch{epoch}"]
-        assert buf.raw[:64].hex() == e[f"light_cache_first64_epoch{epoch}"]
-        assert buf.raw[-64:].hex() == e[f"light_cache_last64_epoch{epoch}"]
-        print(f"epoch {epoch}: host light cache {dt:.2f} s")
+        for which, name in ((0, "dispatch"), (1, "scalar"), (2, "avx512")):
+            if epoch == 448 and which == 0:
+                continue  # same code as one of the other two
+            buf = C.create_string_buffer(n * 64)
+            t = time.time()
+            rc = lib.nx_host_light_cache_variant(epoch, which, buf)
+            dt = time.time() - t
+            if rc == -1:
+                assert which == 2  # CPU without AVX-512F
+                continue
+            assert hashlib.sha256(buf.raw).hexdigest() == e[f"light_cache_sha256_epoch{epoch}"], name
+            assert buf.raw[:64].hex() == e[f"light_cache_first64_epoch{epoch}"]
+            assert buf.raw[-64:].hex() == e[f"light_cache_last64_epoch{epoch}"]
+            print(f"epoch {epoch}: host light cache ({name}) {dt:.2f} s")
+
+
+def test_avx512_keccak_equals_scalar():
+    rnd = random.Random(4)
+    for _ in range(50):
+        st = [rnd.getrandbits(64) for _ in range(25)]
+        a, b = (C.c_uint64 * 25)(*st), (C.c_uint64 * 25)(*st)
+        lib.nx_keccakf1600(a)
+        if lib.nx_keccakf1600_avx512(b) == -1:
+            return  # no AVX-512F on this CPU
+        assert list(a) == list(b)
+    z = (C.c_uint64 * 25)()
+    lib.nx_keccakf1600_avx512(z)
+    assert z[0] == 0xF1258F7940E1DDE7  # Keccak-f[1600] of the all-zero state, first lane
