@@ -65,6 +65,14 @@ def main():
     t0 = time.perf_counter()
     ok = progpow.verify_batch(ctx, vrecs)
     res["K6_verify_batch"] = {"records": len(vrecs), "all_valid": all(ok), "e2e_kHs": len(vrecs) / (time.perf_counter() - t0) / 1e3}
+    # single-header latency: what the node's validation thread sees per block (progpow::hash at its own height)
+    singles = [(height + rnd.randrange(7500), rnd.randbytes(32), rnd.getrandbits(64)) for _ in range(300)]
+    progpow.hash(ctx, *singles[0])
+    t0 = time.perf_counter()
+    for r in singles:
+        progpow.hash(ctx, *r)
+    res["single_hash_latency_us"] = {"mean": (time.perf_counter() - t0) / len(singles) * 1e6, "calls": len(singles),
+                                     "path": "nx_kawpow_hash -> interpreted kernel K6 (uncompiled period), via ctypes"}
     # K7 classic Ethash
     n7 = 1 << 20
     ethash.hash_batch(ctx, hd, 0, 1 << 12)
