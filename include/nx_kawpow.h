@@ -262,8 +262,8 @@ int nx_check_proof_of_work(const uint8_t final_hash[32], uint32_t bits, const ui
 /* ------------------------------------------------------------------------------------------------
  * Miner: one process, all GPUs.  Replaces the nonce loops of miner.cpp:656-713 (CloreMiner) and
  * rpc/mining.cpp:117-173 (generateBlocks), and the epoch-context handling of hash.cpp:260-266 /
- * crypto/ethash/lib/ethash/managed.cpp.  Nonce super-batches are dealt round-robin to the devices; the
- * result is the LOWEST qualifying nonce of the range (host-side min reduction, progpow.cpp:572-577). */
+ * crypto/ethash/lib/ethash/managed.cpp.  Devices claim nonce super-batches in ascending order as they become
+ * free; the result is the LOWEST qualifying nonce of the range (host-side min reduction, progpow.cpp:572-577). */
 typedef struct nx_miner nx_miner;
 int nx_miner_create(const int* devices, int n_devices, nx_miner** out); /* devices NULL / n 0 = all visible GPUs */
 void nx_miner_destroy(nx_miner* m);
@@ -280,6 +280,9 @@ const nx_epoch* nx_miner_context(const nx_miner* m, int index);          /* borr
 int nx_miner_search(nx_miner* m, int block_number, const uint8_t header_hash[32], const uint8_t boundary[32],
                     uint64_t start_nonce, uint64_t iterations, const volatile int* cancel, nx_search_result* out);
 int nx_miner_last_stats(const nx_miner* m, uint64_t* hashes, double* seconds);
+/* Devices that failed during the last search; their windows were re-issued to the surviving devices (the call
+ * only fails when no device is left). */
+int nx_miner_last_failed_devices(const nx_miner* m);
 /* Header fields in, nBits decoded, nNonce64 scanned: the body of miner.cpp:656-690 in one call. */
 int nx_miner_mine_header(nx_miner* m, int32_t version, const uint8_t prev_block[32], const uint8_t merkle_root[32],
                          uint32_t time, uint32_t bits, uint32_t height, uint64_t start_nonce, uint64_t max_tries,

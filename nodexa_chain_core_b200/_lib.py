@@ -113,6 +113,7 @@ def _load() -> C.CDLL:
         "nx_miner_prepared_epoch": (i, [vp]),
         "nx_miner_context": (vp, [vp, i]),
         "nx_miner_search": (i, [vp, i, u8p, u8p, u64, u64, C.POINTER(i), C.POINTER(NxSearchResult)]),
+        "nx_miner_last_failed_devices": (i, [vp]),
         "nx_miner_last_stats": (i, [vp, C.POINTER(u64), C.POINTER(C.c_double)]),
         "nx_miner_mine_header": (i, [vp, C.c_int32, u8p, u8p, u32, u32, u32, u64, u64, C.POINTER(i),
                                      C.POINTER(NxSearchResult)]),

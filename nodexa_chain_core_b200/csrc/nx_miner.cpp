@@ -4,9 +4,10 @@
 //
 //  * one epoch context per device; the (serial) light cache is built ONCE on the host and shared, every device
 //    then generates its own DAG copy in parallel (0.2 s on a B200 - cheaper than moving 4.5 GiB around);
-//  * nonce space cut into super-batches of `batch` nonces, device g of N scans batch k*N+g; the answer is the
-//    LOWEST qualifying nonce (progpow.cpp:572-577), so a device keeps going until its next window lies above
-//    the best hit so far - a host-side min reduction, no device collective;
+//  * nonce space cut into super-batches of `batch` nonces that the devices claim in ascending order as they
+//    become free; the answer is the LOWEST qualifying nonce (progpow.cpp:572-577): windows above the best hit so
+//    far are dropped, windows below it finish - a host-side min reduction, no device collective.  A device whose
+//    launch fails drops out and its window returns to the pool for the surviving devices;
 //  * nx_miner_prepare_async() builds the next epoch's contexts and NVRTC-compiles the next period's program
 //    in a background thread, so neither ever sits on the mining path.
 #include "nx_internal.hpp"
@@ -34,6 +35,7 @@ struct nx_miner
     // statistics of the last search
     std::atomic<uint64_t> hashes{0};
     double last_seconds = 0;
+    int failed_devices = 0;             // devices that dropped out during the last search
 };
 
 namespace
@@ -291,34 +293,70 @@ int nx_miner_search(nx_miner* m, int block_number, const uint8_t header_hash[32]
     const uint64_t total_batches = (iterations + B - 1) / B;
     std::atomic<uint64_t> best_offset{~0ull};  // lowest hit so far, as an offset from start_nonce
     std::atomic<uint64_t> scanned{0};
+    std::atomic<uint64_t> next_batch{0};       // windows are claimed in ascending order by whichever device is free
+    std::mutex retry_mu;
+    std::vector<uint64_t> retry;               // windows given back by a device that failed
     std::vector<int> rcs(n, NX_OK);
     std::vector<std::string> errs(n);
     std::vector<nx_search_result> hits(n);
+    std::atomic<int> alive{(int)n};
     const auto t0 = std::chrono::steady_clock::now();
+
+    // test hook: NX_MINER_INJECT_FAIL="<device index>:<windows it may complete first>"
+    int fail_dev = -1;
+    long fail_after = 0;
+    if (const char* e = std::getenv("NX_MINER_INJECT_FAIL")) {
+        char* end = nullptr;
+        fail_dev = (int)std::strtol(e, &end, 10);
+        if (end && *end == ':') fail_after = std::strtol(end + 1, nullptr, 10);
+    }
 
     auto worker = [&](size_t g) {
         std::memset(&hits[g], 0, sizeof hits[g]);
-        for (uint64_t k = g; k < total_batches; k += n) {
+        long done_here = 0;
+        for (;;) {
+            uint64_t k;
+            {
+                std::lock_guard<std::mutex> lk(retry_mu);
+                if (!retry.empty()) {
+                    k = retry.back();
+                    retry.pop_back();
+                } else {
+                    k = next_batch.fetch_add(1, std::memory_order_relaxed);
+                }
+            }
+            if (k >= total_batches) break;
             const uint64_t off = k * B;
-            if (off >= best_offset.load(std::memory_order_relaxed)) break;  // everything from here on is above the best hit
+            // Windows are handed out in ascending order, so once a hit exists every window starting above it can
+            // be dropped; windows below it that are still running on other devices finish and may lower it.
+            if (off >= best_offset.load(std::memory_order_relaxed)) continue;
             if (cancel && *cancel) break;
             const uint64_t count = iterations - off < B ? iterations - off : B;
             nx_search_result r;
-            int e = nx_kawpow_search_enqueue(ctxs[g], block_number, header_hash, boundary, start_nonce + off, count);
+            int e = NX_OK;
+            if ((int)g == fail_dev && done_here >= fail_after) {
+                set_error("injected failure (NX_MINER_INJECT_FAIL)");
+                e = NX_ERR_CUDA;
+            }
+            if (e == NX_OK) e = nx_kawpow_search_enqueue(ctxs[g], block_number, header_hash, boundary, start_nonce + off, count);
             if (e == NX_OK) e = nx_kawpow_search_sync(ctxs[g], &r);
             if (e != NX_OK) {
+                // this device drops out; its window goes back to the pool for the surviving devices
                 rcs[g] = e;
                 errs[g] = nx_last_error();
+                std::lock_guard<std::mutex> lk(retry_mu);
+                retry.push_back(k);
+                alive.fetch_sub(1);
                 return;
             }
+            ++done_here;
             scanned.fetch_add(count, std::memory_order_relaxed);
             if (r.found) {
                 const uint64_t hit_off = r.nonce - start_nonce;
                 uint64_t cur = best_offset.load();
                 while (hit_off < cur && !best_offset.compare_exchange_weak(cur, hit_off)) {
                 }
-                hits[g] = r;
-                break;  // later windows of this device are all above this hit
+                if (!hits[g].found || r.nonce - start_nonce < hits[g].nonce - start_nonce) hits[g] = r;
             }
         }
     };
@@ -326,19 +364,31 @@ int nx_miner_search(nx_miner* m, int block_number, const uint8_t header_hash[32]
     for (size_t g = 1; g < n; ++g) th.emplace_back(worker, g);
     worker(0);
     for (auto& t : th) t.join();
+    // A device may have failed after the others had already run out of windows: finish its window(s) on a survivor.
+    for (size_t g = 0; g < n && !retry.empty(); ++g)
+        if (rcs[g] == NX_OK) {
+            const nx_search_result keep = hits[g];
+            worker(g);
+            if (keep.found && (!hits[g].found || keep.nonce - start_nonce < hits[g].nonce - start_nonce)) hits[g] = keep;
+        }
     m->last_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     m->hashes = scanned.load();
-    for (size_t g = 0; g < n; ++g)
-        if (rcs[g] != NX_OK) {
-            set_error("device %d: %s", m->devices[g], errs[g].c_str());
-            return rcs[g];
-        }
+    m->failed_devices = (int)n - alive.load();
+    if (!retry.empty() || alive.load() == 0) {  // nobody left to take the work over
+        for (size_t g = 0; g < n; ++g)
+            if (rcs[g] != NX_OK) {
+                set_error("device %d: %s", m->devices[g], errs[g].c_str());
+                return rcs[g];
+            }
+    }
     const uint64_t best = best_offset.load();
     if (best == ~0ull) return NX_OK;
     for (size_t g = 0; g < n; ++g)
         if (hits[g].found && hits[g].nonce - start_nonce == best) *out = hits[g];
     return NX_OK;
 }
+
+int nx_miner_last_failed_devices(const nx_miner* m) { return m ? m->failed_devices : 0; }
 
 int nx_miner_last_stats(const nx_miner* m, uint64_t* hashes, double* seconds)
 {

@@ -63,6 +63,10 @@ class Miner:
                                        start_nonce, max_tries, C.byref(self._cancel), C.byref(r)))
         return _sr(r)
 
+    @property
+    def last_failed_devices(self) -> int:
+        return lib.nx_miner_last_failed_devices(self._h)
+
     def last_stats(self):
         n, s = C.c_uint64(), C.c_double()
         lib.nx_miner_last_stats(self._h, C.byref(n), C.byref(s))

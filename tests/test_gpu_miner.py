@@ -69,3 +69,28 @@ def test_background_prepare_next_epoch(nx):
         r1 = m.search(7500, hd, b"\xff" * 32, 0, 1)  # adopts the prebuilt epoch-1 contexts
         assert m.epoch == 1 and m.prepared_epoch == -1 and r1.solution_found
         assert r1.final_hash != r0.final_hash
+
+
+def test_failed_device_drops_out_and_its_windows_are_reissued(nx, ctx_of, monkeypatch):
+    """Failure handling: a device whose launch fails leaves the search, its window goes back to the pool, and the
+    answer is still the lowest nonce.  Needs two GPUs to have a survivor; with one GPU the call must fail loudly."""
+    ctx = ctx_of(0)
+    hd = hashlib.sha256(b"failover").digest()
+    boundary = ((1 << (256 - 18)) - 1).to_bytes(32, "big")
+    n = 1 << 20
+    want = progpow.search(ctx, 900, hd, boundary, 1 << 50, n)
+    ndev = nx.lib.nx_device_count()
+    with nx.Miner() as m:
+        m.set_batch(1 << 14)
+        m.set_epoch(0)
+        monkeypatch.setenv("NX_MINER_INJECT_FAIL", f"{ndev - 1}:2")  # last device fails on its third window
+        if ndev >= 2:
+            got = m.search(900, hd, boundary, 1 << 50, n)
+            assert got == want
+            assert m.last_failed_devices == 1
+        else:
+            with pytest.raises(nx.NxError):
+                m.search(900, hd, bytes(32), 1 << 50, n)
+            assert m.last_failed_devices == 1
+        monkeypatch.delenv("NX_MINER_INJECT_FAIL")
+        assert m.search(900, hd, boundary, 1 << 50, n) == want and m.last_failed_devices == 0
