@@ -66,6 +66,38 @@ int check_ctx(const nx_epoch* c, int block_number)
     return NX_OK;
 }
 
+// K3 gathers 512 random 64-byte parents per item from the light cache (16-80 MiB).  It only just fits the 126 MB
+// L2, and on a two-die part a plain LRU keeps ~76 % of it resident; marking the window as persisting while the DAG
+// is generated keeps the gather in L2.  Best effort: unsupported or refused settings are ignored.
+void l2_pin_light_cache(nx_epoch* c, bool on)
+{
+    if (const char* e = std::getenv("NX_NO_L2_PIN"))
+        if (*e && *e != '0') return;
+    cudaStreamAttrValue attr;
+    std::memset(&attr, 0, sizeof attr);
+    if (on) {
+        int max_persist = 0, max_window = 0;
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, c->device);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
+        if (max_persist <= 0 || max_window <= 0) return;
+        const size_t light_bytes = (size_t)c->light_items * 64;
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist);
+        const size_t window = light_bytes < (size_t)max_window ? light_bytes : (size_t)max_window;
+        attr.accessPolicyWindow.base_ptr = c->light_dev;
+        attr.accessPolicyWindow.num_bytes = window;
+        attr.accessPolicyWindow.hitRatio = (float)((size_t)max_persist >= window ? 1.0 : (double)max_persist / (double)window);
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    } else {
+        attr.accessPolicyWindow.num_bytes = 0;
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+    }
+    cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr);
+    if (!on) cudaCtxResetPersistingL2Cache();
+    cudaGetLastError();
+}
+
 int program_for(const nx_epoch* c, int block_number, std::shared_ptr<KawpowProgram>* p)
 {
     return kawpow_get_program(c->device, (uint64_t)(block_number / NX_PERIOD_LENGTH), c->dag_items, p);
@@ -180,6 +212,7 @@ int create(int epoch, int device, int rank, int world, const uint8_t* light_in, 
                                c->dag_padded_bytes - (size_t)c->dag_items * 256, c->stream));
     c->deferred = deferred;
     if (!deferred) {
+        l2_pin_light_cache(c, true);
         NX_TRY(cudaEventRecord(c->ev0, c->stream));
         int rc = dag_generate(c->light_dev, c->light_items, first, count, (char*)c->dag_dev + (size_t)first * 256,
                               c->stream);
@@ -187,6 +220,7 @@ int create(int epoch, int device, int rank, int world, const uint8_t* light_in, 
         NX_TRY(cudaEventRecord(c->ev1, c->stream));
     }
     NX_TRY(cudaStreamSynchronize(c->stream));
+    if (!deferred) l2_pin_light_cache(c, false);
     if (!deferred) {
         float ms = 0;
         NX_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
@@ -268,11 +302,13 @@ static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries;
         if (r != c->rank) outs[n++] = (char*)peer_bases[r] + (size_t)first * 256;
     std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
+    l2_pin_light_cache(c, true);
     NX_CUDA(cudaEventRecord(c->ev0, c->stream));
     const int rc = dag_generate_multi(c->light_dev, c->light_items, first, count, outs, n, c->stream);
     if (rc != NX_OK) return rc;
     NX_CUDA(cudaEventRecord(c->ev1, c->stream));
     NX_CUDA(cudaStreamSynchronize(c->stream));
+    l2_pin_light_cache(c, false);
     float ms = 0;
     NX_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     c->dag_ms = ms;
@@ -367,11 +403,13 @@ int nx_dag_generate_range(const nx_epoch* cc, uint32_t first, uint32_t count, vo
     }
     std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
+    l2_pin_light_cache(c, true);
     NX_CUDA(cudaEventRecord(c->ev0, c->stream));
     int rc = dag_generate(c->light_dev, c->light_items, first, count, out_device, c->stream);
     if (rc != NX_OK) return rc;
     NX_CUDA(cudaEventRecord(c->ev1, c->stream));
     NX_CUDA(cudaStreamSynchronize(c->stream));
+    l2_pin_light_cache(c, false);
     NX_CUDA(cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1));
     c->last_launches = 1;
     return NX_OK;
