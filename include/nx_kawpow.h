@@ -260,6 +260,43 @@ int nx_compact_to_boundary(uint32_t bits, uint8_t out[32]);
 int nx_check_proof_of_work(const uint8_t final_hash[32], uint32_t bits, const uint8_t pow_limit_be[32]);
 
 /* ------------------------------------------------------------------------------------------------
+ * Wire format: the 120-byte block header of KawPow blocks (primitives/block.h:36-74 with
+ * nTime >= nKAWPOWActivationTime): nVersion i32 | hashPrevBlock[32] | hashMerkleRoot[32] | nTime u32 | nBits u32 |
+ * nHeight u32 | nNonce64 u64 | mix_hash[32], integers little-endian, uint256 fields in storage order (i.e. the
+ * byte-reverse of the hash256 strings the progpow functions use, see hash.cpp:269-276). */
+typedef struct nx_block_header
+{
+    int32_t version;
+    uint8_t prev_block[32];
+    uint8_t merkle_root[32];
+    uint32_t time;
+    uint32_t bits;
+    uint32_t height;
+    uint64_t nonce64;
+    uint8_t mix_hash[32]; /* uint256 storage order, as on the wire */
+} nx_block_header;
+void nx_block_header_parse(const uint8_t raw[120], nx_block_header* out);
+void nx_block_header_serialize(const nx_block_header* in, uint8_t raw[120]);
+/* Block id of a KawPow block = CBlockHeader::GetHash() = KAWPOWHash_OnlyMix (primitives/block.cpp:38-55,
+ * hash.cpp:280-291): final hash from the header's own mix_hash, returned in uint256 storage order. Host only. */
+void nx_block_hash(const uint8_t raw[120], uint8_t out_uint256[32]);
+
+/* PoW part of CheckBlockHeader (validation.cpp:11638-11665) for n wire headers of ONE epoch, in one K6 launch.
+ *   mix_only = 1: the below-checkpoint branch (:11641-11649): CheckProofOfWork(GetHash()) only, no GPU work;
+ *   mix_only = 0: CheckProofOfWork(GetHashFull(mix)) with the RECOMPUTED final hash, then mix == header.mix_hash.
+ * status[i]: */
+enum
+{
+    NX_HEADER_OK = 0,
+    NX_HEADER_HIGH_HASH = 1,        /* "high-hash": proof of work failed */
+    NX_HEADER_INVALID_MIX = 2,      /* "invalid-mix-hash" */
+    NX_HEADER_BAD_BITS = 3,         /* nBits negative / zero / overflow / above pow_limit (pow.cpp:190-191) */
+    NX_HEADER_WRONG_EPOCH = 4       /* nHeight is not in the context's epoch: not checked */
+};
+int nx_check_block_headers(const nx_epoch* ctx, const uint8_t* raw_headers /* n x 120 */, size_t n,
+                           const uint8_t pow_limit_be[32], int mix_only, uint8_t* status);
+
+/* ------------------------------------------------------------------------------------------------
  * Miner: one process, all GPUs.  Replaces the nonce loops of miner.cpp:656-713 (CloreMiner) and
  * rpc/mining.cpp:117-173 (generateBlocks), and the epoch-context handling of hash.cpp:260-266 /
  * crypto/ethash/lib/ethash/managed.cpp.  Devices claim nonce super-batches in ascending order as they become

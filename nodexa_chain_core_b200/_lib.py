@@ -34,6 +34,12 @@ class NxHashRecord(C.Structure):
     _fields_ = [("block_number", C.c_int32), ("pad", C.c_uint32), ("nonce", C.c_uint64), ("header_hash", C.c_uint8 * 32)]
 
 
+class NxBlockHeader(C.Structure):
+    _fields_ = [("version", C.c_int32), ("prev_block", C.c_uint8 * 32), ("merkle_root", C.c_uint8 * 32),
+                ("time", C.c_uint32), ("bits", C.c_uint32), ("height", C.c_uint32), ("nonce64", C.c_uint64),
+                ("mix_hash", C.c_uint8 * 32)]
+
+
 class NxVerifyRecord(C.Structure):
     _fields_ = [("block_number", C.c_int32), ("pad", C.c_uint32), ("nonce", C.c_uint64),
                 ("header_hash", C.c_uint8 * 32), ("mix_hash", C.c_uint8 * 32), ("boundary", C.c_uint8 * 32)]
@@ -102,6 +108,10 @@ def _load() -> C.CDLL:
         "nx_sha256d": (None, [u8p, sz, u8p]),
         "nx_compact_to_boundary": (i, [u32, u8p]),
         "nx_check_proof_of_work": (i, [u8p, u32, u8p]),
+        "nx_block_header_parse": (None, [u8p, C.POINTER(NxBlockHeader)]),
+        "nx_block_header_serialize": (None, [C.POINTER(NxBlockHeader), u8p]),
+        "nx_block_hash": (None, [u8p, u8p]),
+        "nx_check_block_headers": (i, [vp, u8p, sz, u8p, i, u8p]),
         "nx_miner_create": (i, [C.POINTER(i), i, C.POINTER(vp)]),
         "nx_miner_destroy": (None, [vp]),
         "nx_miner_device_count": (i, [vp]),

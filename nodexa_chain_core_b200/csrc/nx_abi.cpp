@@ -806,6 +806,67 @@ int nx_kawpow_hash_many(const nx_epoch* cc, const nx_hash_record* records, size_
     return NX_OK;
 }
 
+int nx_check_block_headers(const nx_epoch* c, const uint8_t* raw, size_t n, const uint8_t pow_limit_be[32], int mix_only,
+                           uint8_t* status)
+{
+    if ((!raw || !status) && n) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    int rc = check_ctx(c, 0);
+    if (rc != NX_OK) return rc;
+    std::vector<nx_hash_record> todo;
+    std::vector<size_t> index;
+    std::vector<uint8_t> targets;  // 32 bytes per surviving header
+    for (size_t i = 0; i < n; ++i) {
+        const uint8_t* h = raw + 120 * i;
+        nx_block_header f;
+        nx_block_header_parse(h, &f);
+        uint8_t target[32];
+        if (!nx_compact_to_boundary(f.bits, target) || (pow_limit_be && std::memcmp(target, pow_limit_be, 32) > 0)) {
+            status[i] = NX_HEADER_BAD_BITS;
+            continue;
+        }
+        if (mix_only) {  // below the last checkpoint: the final hash from the header's own mix is enough
+            uint8_t id[32], fin[32];
+            nx_block_hash(h, id);
+            for (int k = 0; k < 32; ++k) fin[k] = id[31 - k];
+            status[i] = std::memcmp(fin, target, 32) <= 0 ? NX_HEADER_OK : NX_HEADER_HIGH_HASH;
+            continue;
+        }
+        if ((int)(f.height / NX_EPOCH_LENGTH) != c->epoch || (int32_t)f.height < 0) {
+            status[i] = NX_HEADER_WRONG_EPOCH;
+            continue;
+        }
+        nx_hash_record r;
+        r.block_number = (int32_t)f.height;
+        r.pad = 0;
+        r.nonce = f.nonce64;
+        uint8_t d[32];
+        nx_sha256d(h, 80, d);
+        for (int k = 0; k < 32; ++k) r.header_hash[k] = d[31 - k];
+        todo.push_back(r);
+        index.push_back(i);
+        targets.insert(targets.end(), target, target + 32);
+    }
+    if (todo.empty()) return NX_OK;
+    std::vector<uint8_t> out(todo.size() * 64);
+    if ((rc = nx_kawpow_hash_many(c, todo.data(), todo.size(), out.data())) != NX_OK) return rc;
+    for (size_t k = 0; k < todo.size(); ++k) {
+        const uint8_t* fin = out.data() + 64 * k;
+        const uint8_t* mix = fin + 32;
+        const uint8_t* claimed = raw + 120 * index[k] + 88;  // uint256 storage order = reversed
+        if (std::memcmp(fin, targets.data() + 32 * k, 32) > 0) {
+            status[index[k]] = NX_HEADER_HIGH_HASH;
+            continue;
+        }
+        bool same = true;
+        for (int b = 0; b < 32; ++b) same &= mix[b] == claimed[31 - b];
+        status[index[k]] = same ? NX_HEADER_OK : NX_HEADER_INVALID_MIX;
+    }
+    return NX_OK;
+}
+
 int nx_kawpow_verify_batch(const nx_epoch* c, const nx_verify_record* records, size_t n, uint8_t* ok)
 {
     if ((!records || !ok) && n) {

@@ -236,6 +236,45 @@ void nx_kawpow_header_hash(int32_t version, const uint8_t prev_block[32], const 
     for (int i = 0; i < 32; ++i) out[i] = d[31 - i];
 }
 
+void nx_block_header_parse(const uint8_t raw[120], nx_block_header* out)
+{
+    std::memcpy(&out->version, raw, 4);
+    std::memcpy(out->prev_block, raw + 4, 32);
+    std::memcpy(out->merkle_root, raw + 36, 32);
+    std::memcpy(&out->time, raw + 68, 4);
+    std::memcpy(&out->bits, raw + 72, 4);
+    std::memcpy(&out->height, raw + 76, 4);
+    std::memcpy(&out->nonce64, raw + 80, 8);
+    std::memcpy(out->mix_hash, raw + 88, 32);
+}
+
+void nx_block_header_serialize(const nx_block_header* in, uint8_t raw[120])
+{
+    std::memcpy(raw, &in->version, 4);
+    std::memcpy(raw + 4, in->prev_block, 32);
+    std::memcpy(raw + 36, in->merkle_root, 32);
+    std::memcpy(raw + 68, &in->time, 4);
+    std::memcpy(raw + 72, &in->bits, 4);
+    std::memcpy(raw + 76, &in->height, 4);
+    std::memcpy(raw + 80, &in->nonce64, 8);
+    std::memcpy(raw + 88, in->mix_hash, 32);
+}
+
+void nx_block_hash(const uint8_t raw[120], uint8_t out_uint256[32])
+{
+    // the first 80 bytes of the wire header ARE the CKAWPOWInput (block.h:213-233)
+    uint8_t d[32], header_hash[32], mix[32], fin[32];
+    nx_sha256d(raw, 80, d);
+    for (int i = 0; i < 32; ++i) header_hash[i] = d[31 - i];
+    for (int i = 0; i < 32; ++i) mix[i] = raw[88 + 31 - i];
+    uint64_t nonce;
+    uint32_t height;
+    std::memcpy(&nonce, raw + 80, 8);
+    std::memcpy(&height, raw + 76, 4);
+    nx_kawpow_hash_no_verify((int)height, header_hash, mix, nonce, fin);
+    for (int i = 0; i < 32; ++i) out_uint256[i] = fin[31 - i];
+}
+
 int nx_compact_to_boundary(uint32_t bits, uint8_t out[32])
 {
     const int size = (int)(bits >> 24);

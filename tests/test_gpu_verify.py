@@ -84,3 +84,49 @@ def test_verify_batch_semantics(nx, ctx_of):
     assert progpow.verify_batch(ctx, []) == []
     with pytest.raises(nx.NxError):  # a block outside the context's epoch is refused, not mis-hashed
         progpow.hash_many(ctx, [(7500, bytes(32), 0)])
+
+
+def test_check_block_headers_like_the_node(nx, ctx_of, oracle):
+    """validation.cpp:11638-11665 on wire headers: mine a few synthetic blocks on the GPU, serialise them as the
+    node would (120 bytes), then check them in one batch - untouched, with a wrong nonce, with a wrong mix, with a
+    target above powLimit, from another epoch, and through the below-checkpoint (mix-only) branch."""
+    from nodexa_chain_core_b200 import node
+    ctx = ctx_of(0)
+    rnd = random.Random(2026)
+    bits = 0x2000ffff  # target 00ffff00..: about one nonce in 256 qualifies
+    good = []
+    with nx.Miner([0]) as m:
+        m.set_batch(1 << 12)
+        for i in range(6):
+            h = node.BlockHeader(0x30000000, rnd.randbytes(32), rnd.randbytes(32), node.MAINNET_KAWPOW_ACTIVATION_TIME + 60 * i,
+                                 bits, 1000 + 7 * i)
+            sr = m.mine_header(h.version, h.prev_block, h.merkle_root, h.time, h.bits, h.height, start_nonce=i << 32,
+                               max_tries=1 << 16)
+            assert sr.solution_found
+            h.nonce64, h.mix_hash = sr.nonce, sr.mix_hash[::-1]  # uint256S(to_hex(mix)): stored byte-reversed
+            # the oracle agrees with every field the node would store and compare
+            f, mx = oracle.kawpow_hash(0, h.height, h.kawpow_header_hash(), h.nonce64)
+            assert (f, mx) == (sr.final_hash, sr.mix_hash)
+            assert h.block_hash() == f[::-1]          # GetHash() of a valid block equals the full PoW hash
+            assert node.check_proof_of_work(f, bits)
+            good.append(h)
+    assert node.check_block_headers(ctx, good) == [node.HEADER_OK] * len(good)
+    assert node.check_block_headers(ctx, good, mix_only=True) == [node.HEADER_OK] * len(good)
+    assert node.check_block_headers(ctx, []) == []
+
+    import copy
+    bad_nonce = copy.copy(good[0]); bad_nonce.nonce64 ^= 1
+    bad_mix = copy.copy(good[1]); bad_mix.mix_hash = bytes([good[1].mix_hash[0] ^ 1]) + good[1].mix_hash[1:]
+    bad_bits = copy.copy(good[2]); bad_bits.bits = 0x207fffff        # regtest-sized target > kawpowLimit
+    zero_bits = copy.copy(good[2]); zero_bits.bits = 0
+    other_epoch = copy.copy(good[3]); other_epoch.height = 7500
+    got = node.check_block_headers(ctx, [bad_nonce, bad_mix, bad_bits, zero_bits, other_epoch, good[4]])
+    f_bad, _ = oracle.kawpow_hash(0, bad_nonce.height, bad_nonce.kawpow_header_hash(), bad_nonce.nonce64)
+    ok_t, target = oracle.compact_to_boundary(bits)
+    expect_bad_nonce = node.HEADER_INVALID_MIX if f_bad <= target else node.HEADER_HIGH_HASH
+    assert got == [expect_bad_nonce, node.HEADER_INVALID_MIX, node.HEADER_BAD_BITS, node.HEADER_BAD_BITS,
+                   node.HEADER_WRONG_EPOCH, node.HEADER_OK]
+    # mix-only branch: a wrong mix changes the block id, which then (almost surely) misses the target
+    got = node.check_block_headers(ctx, [bad_mix, good[5]], mix_only=True)
+    fin = oracle.kawpow_hash_no_verify(bad_mix.height, bad_mix.kawpow_header_hash(), bad_mix.mix_hash[::-1], bad_mix.nonce64)
+    assert got == [node.HEADER_OK if fin <= target else node.HEADER_HIGH_HASH, node.HEADER_OK]

@@ -133,3 +133,27 @@ def test_avx512_keccak_equals_scalar():
     z = (C.c_uint64 * 25)()
     lib.nx_keccakf1600_avx512(z)
     assert z[0] == 0xF1258F7940E1DDE7  # Keccak-f[1600] of the all-zero state, first lane
+
+
+def test_wire_header_parse_serialize_and_block_hash(oracle):
+    """120-byte KawPow header (primitives/block.h:61-74), CKAWPOWInput hash (block.cpp:94-99 + hash.cpp:269-270)
+    and the block id (GetHash = KAWPOWHash_OnlyMix, hash.cpp:280-291), against the oracle's pieces."""
+    from nodexa_chain_core_b200.node import BlockHeader
+    from nodexa_chain_core_b200._lib import NxBlockHeader
+    rnd = random.Random(12)
+    for _ in range(20):
+        h = BlockHeader(rnd.getrandbits(31), rnd.randbytes(32), rnd.randbytes(32), rnd.getrandbits(32), rnd.getrandbits(32),
+                        rnd.getrandbits(31), rnd.getrandbits(64), rnd.randbytes(32))
+        raw = h.serialize()
+        assert len(raw) == 120 and BlockHeader.parse(raw) == h
+        f = NxBlockHeader()
+        lib.nx_block_header_parse(inb(raw), C.byref(f))
+        assert (f.version, bytes(f.prev_block), bytes(f.merkle_root), f.time, f.bits, f.height, f.nonce64, bytes(f.mix_hash)) == \
+               (h.version, h.prev_block, h.merkle_root, h.time, h.bits, h.height, h.nonce64, h.mix_hash)
+        back = outb(120)
+        lib.nx_block_header_serialize(C.byref(f), back)
+        assert bytes(back) == raw
+        hh = oracle.kawpow_header_hash(h.version, h.prev_block, h.merkle_root, h.time, h.bits, h.height)
+        assert h.kawpow_header_hash() == hh
+        fin = oracle.kawpow_hash_no_verify(h.height, hh, h.mix_hash[::-1], h.nonce64)
+        assert h.block_hash() == fin[::-1]
