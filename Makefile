@@ -9,7 +9,7 @@ LIB       := $(PKG)/libnxkawpow.so
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function,-Wno-unknown-pragmas -Iinclude -I$(SRC)
 CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_src.cpp nx_tools.cpp nx_compat.cpp nx_miner.cpp
-CUSRC     := nx_dag.cu nx_kawpow_interp.cu
+CUSRC     := nx_dag.cu nx_kawpow_interp.cu nx_equihash.cu
 OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o)) $(OBJ)/nx_lightcache_avx512.o $(OBJ)/nx_cpu_dispatch.o
 
 .PHONY: all lib oracle ref clean
@@ -22,6 +22,7 @@ $(SRC)/kawpow_kernel_src.inc: $(SRC)/kawpow_kernel.cuh
 
 $(OBJ)/nx_kernel_src.o: $(SRC)/kawpow_kernel_src.inc
 $(OBJ)/nx_kawpow_interp.o: $(SRC)/kawpow_kernel.cuh
+$(OBJ)/nx_equihash.o: $(SRC)/nx_blake2b.cuh include/nx_equihash.h
 
 # plain host code built by g++ directly: the AVX-512 light-cache chain (only called when the CPU has AVX-512F)
 $(OBJ)/nx_lightcache_avx512.o: $(SRC)/nx_lightcache_avx512.cpp

@@ -5,7 +5,7 @@ behaviour follow src/crypto/ethash/include/ethash/{ethash.hpp,progpow.hpp} of
 DeonDavisV/Nodexa-Chain-Core); every call goes through the C ABI in include/nx_kawpow.h to
 hand-written CUDA for sm_100a.  There is no CPU fallback.
 """
-from . import ethash, node, progpow, sharding  # noqa: F401
+from . import equihash, ethash, node, progpow, sharding  # noqa: F401
 from .miner import Miner  # noqa: F401
 from ._lib import LIB_PATH, NxError, lib  # noqa: F401
 from .ethash import (EpochContext, calculate_epoch_seed, calculate_full_dataset_num_items,  # noqa: F401

@@ -127,6 +127,13 @@ def _load() -> C.CDLL:
         "nx_miner_last_stats": (i, [vp, C.POINTER(u64), C.POINTER(C.c_double)]),
         "nx_miner_mine_header": (i, [vp, C.c_int32, u8p, u8p, u32, u32, u32, u64, u64, C.POINTER(i),
                                      C.POINTER(NxSearchResult)]),
+        # gated Equihash engine (include/nx_equihash.h; no reference counterpart)
+        "nx_equihash_solution_bytes": (sz, [i, i]),
+        "nx_equihash_create": (i, [i, i, i, u8p, C.POINTER(vp)]),
+        "nx_equihash_destroy": (None, [vp]),
+        "nx_equihash_solve": (i, [vp, u8p, sz, u8p, i, C.POINTER(i)]),
+        "nx_equihash_validate": (i, [vp, u8p, sz, u8p, i, u8p]),
+        "nx_equihash_last_timing": (i, [vp, C.POINTER(C.c_float), C.POINTER(i)]),
         # introspection (nx_tools.cpp; not part of the drop-in surface)
         "nx_kawpow_program_source": (sz, [u64, u32, i, C.c_char_p, sz]),
         "nx_kawpow_program_ops": (i, [u64, C.POINTER(u32 * 6), i]),

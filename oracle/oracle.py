@@ -50,8 +50,8 @@ class Oracle:
     kind = "port"
 
     def __init__(self):
-        if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
-                os.path.join(HERE, "nx_oracle.c")):
+        srcs = [os.path.join(HERE, f) for f in ("nx_oracle.c", "nx_equihash_oracle.c")]
+        if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
             build_oracle()
         L = self.L = C.CDLL(ORACLE_SO)
         L.nxo_ctx_create.restype = C.POINTER(_Ctx)
@@ -81,7 +81,41 @@ class Oracle:
         L.nxo_compact_to_boundary.argtypes = [C.c_uint32, u8p]
         L.nxo_less_or_equal.argtypes = [u8p, u8p]
         L.nxo_build_light_cache.argtypes = [u8p, C.c_int, u8p]
+        # Equihash self-consistency oracle (nx_equihash_oracle.c; NOT reference-derived)
+        L.nxeq_blake2b.argtypes = [u8p, C.c_size_t, u8p, u8p, C.c_size_t]
+        L.nxeq_solution_bytes.restype = C.c_size_t
+        L.nxeq_solution_bytes.argtypes = [C.c_int, C.c_int]
+        L.nxeq_solve.argtypes = [C.c_int, C.c_int, u8p, u8p, C.c_size_t, u8p, C.c_int]
+        L.nxeq_validate.argtypes = [C.c_int, C.c_int, u8p, u8p, C.c_size_t, u8p]
+        L.nxeq_decode.argtypes = [C.c_int, C.c_int, u8p, C.POINTER(C.c_uint32)]
+        L.nxeq_encode.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_uint32), u8p]
         self._ctx = {}
+
+    # -- Equihash (self-consistency only) --
+    def blake2b(self, data: bytes, personal: bytes, outlen: int) -> bytes:
+        o = _buf(outlen)
+        self.L.nxeq_blake2b(_in(data) if data else _buf(1), len(data), _in(personal), o, outlen)
+        return bytes(o)
+
+    def equihash_solution_bytes(self, n, k) -> int:
+        return self.L.nxeq_solution_bytes(n, k)
+
+    def equihash_solve(self, n, k, tag: bytes, header: bytes, max_solutions: int = 64):
+        sb = self.equihash_solution_bytes(n, k)
+        out = _buf(sb * max_solutions)
+        cnt = self.L.nxeq_solve(n, k, _in(tag), _in(header), len(header), out, max_solutions)
+        if cnt < 0:
+            raise ValueError("bad Equihash parameters")
+        raw = bytes(out)
+        return [raw[i * sb:(i + 1) * sb] for i in range(min(cnt, max_solutions))]
+
+    def equihash_validate(self, n, k, tag: bytes, header: bytes, solution: bytes) -> bool:
+        return bool(self.L.nxeq_validate(n, k, _in(tag), _in(header), len(header), _in(solution)))
+
+    def equihash_decode(self, n, k, solution: bytes):
+        idx = (C.c_uint32 * (1 << k))()
+        self.L.nxeq_decode(n, k, _in(solution), idx)
+        return list(idx)
 
     # -- contexts are cached per epoch (light cache build is ~1 s) --
     def ctx(self, epoch: int):
