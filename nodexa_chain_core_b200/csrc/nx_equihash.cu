@@ -28,7 +28,8 @@ namespace nx
 namespace
 {
 constexpr int EQ_MAX_CHUNKS = 12;      // k+1
-constexpr int EQ_BUCKET_CAP = 1024;    // slots per bucket (mean load 512)
+constexpr int EQ_BUCKET_CAP = 2048;    // slots per bucket (mean load 512; tiny parameter sets have ONE bucket
+                                       // whose load swings widely, hence the generous headroom)
 constexpr int EQ_COLLIDE_THREADS = 256;
 constexpr int EQ_MAX_CANDIDATES = 4096;
 
@@ -67,7 +68,7 @@ __device__ void eq_string_chunks(const EqParams& p, const Blake2bState& mid, uin
 __global__ void eq_generate_kernel(EqParams p, Blake2bState mid, uint32_t* __restrict__ rows)
 {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;  // one digest per thread
-    if (g >= p.N / (uint32_t)p.ipp) return;
+    if (g >= (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp) return;  // N need not be a multiple of 512/n
     Blake2bState s = mid;
     uint8_t le[4] = {(uint8_t)g, (uint8_t)(g >> 8), (uint8_t)(g >> 16), (uint8_t)(g >> 24)};
     b2_update(s, le, 4);
@@ -75,6 +76,7 @@ __global__ void eq_generate_kernel(EqParams p, Blake2bState mid, uint32_t* __res
     b2_final(s, digest);
     for (int j = 0; j < p.ipp; ++j) {
         const uint32_t i = g * (uint32_t)p.ipp + (uint32_t)j;
+        if (i >= p.N) break;
         const uint8_t* str = digest + j * p.hash_bytes;
         for (int c = 0; c < p.chunks; ++c) rows[(size_t)i * p.chunks + c] = eq_chunk(str, p.cbl, c);
     }
@@ -361,7 +363,8 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     s->p = p;
     s->device = device;
     std::memcpy(s->tag, tag, 8);
-    s->cap = p.N + p.N / 2;
+    // rows per round hover around N (count' ~ count^2 / N); relative swings are large only for tiny N
+    s->cap = p.N <= (1u << 12) ? 4 * p.N : p.N + p.N / 2;
     const size_t row_bytes = (size_t)s->cap * p.chunks * 4;
     const uint32_t leaves = 1u << k;
     bool ok = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) == cudaSuccess && cudaEventCreate(&s->ev0) == cudaSuccess &&
@@ -404,7 +407,7 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
 
     NX_CUDA(cudaEventRecord(s->ev0, s->stream));
     NX_CUDA(cudaMemsetAsync(s->counts, 0, (size_t)(k + 2) * 4, s->stream));
-    const uint32_t digests = p.N / (uint32_t)p.ipp;
+    const uint32_t digests = (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp;
     eq_generate_kernel<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0]);
     ++launches;
     NX_CUDA(cudaMemcpyAsync(s->counts, &p.N, 4, cudaMemcpyHostToDevice, s->stream));  // p lives in *s: stays valid

@@ -259,7 +259,7 @@ int nxeq_solve(int n, int k, const uint8_t tag[8], const uint8_t* header, size_t
     if (!eq_init(&p, n, k, tag)) return -1;
     const int C = p.chunks;
     C_sort = C;
-    const size_t cap = (size_t)p.N * 3; /* rows per round stay near N; 3x is generous */
+    const size_t cap = (size_t)p.N * 4; /* rows per round hover around N (count' ~ count^2/N); 4x is generous */
     uint32_t* rows = (uint32_t*)malloc(cap * C * 4);
     uint32_t* next = (uint32_t*)malloc(cap * C * 4);
     uint32_t* order = (uint32_t*)malloc(cap * 4);

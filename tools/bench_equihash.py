@@ -1,0 +1,55 @@
+#!/usr/bin/env python
+"""Equihash solve throughput (Sol/s) of the gated engine on one GPU, next to the CPU oracle on a bounded sample.
+NOT a comparison with the reference: the reference has no Equihash (SURVEY.md §0 Fact 1)."""
+import argparse
+import hashlib
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+TAG = b"NodexaPW"
+
+
+def header(nonce: int) -> bytes:
+    base = hashlib.sha512(b"nodexa-equihash-bench").digest() * 3
+    return base[:108] + nonce.to_bytes(32, "little")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--nonces", type=int, default=64)
+    ap.add_argument("--cpu-nonces", type=int, default=2)
+    a = ap.parse_args()
+    import nodexa_chain_core_b200 as nx
+    from oracle.oracle import Oracle
+    orc = Oracle()
+    res = {"note": "self-consistency only: the reference contains no Equihash; (n,k) and tag are inputs", "runs": []}
+    for n, k in ((200, 9), (144, 5)):
+        with nx.equihash.Solver(n, k, TAG) as s:
+            for w in range(3):
+                s.solve(header(10**6 + w))
+            sols, kernel_ms = 0, 0.0
+            t0 = time.perf_counter()
+            for i in range(a.nonces):
+                got = s.solve(header(i))
+                sols += len(got)
+                kernel_ms += s.last_timing()[0]
+            wall = time.perf_counter() - t0
+            run = {"n": n, "k": k, "nonces": a.nonces, "solutions": sols, "sol_per_s_device": sols / (kernel_ms * 1e-3),
+                   "sol_per_s_e2e": sols / wall, "ms_per_nonce_device": kernel_ms / a.nonces, "ms_per_nonce_e2e": wall / a.nonces * 1e3,
+                   "launches_per_nonce": s.last_timing()[1]}
+            if (n, k) == (200, 9) and a.cpu_nonces:
+                t0 = time.perf_counter()
+                cs = sum(len(orc.equihash_solve(n, k, TAG, header(i))) for i in range(a.cpu_nonces))
+                dt = time.perf_counter() - t0
+                run["cpu_oracle"] = {"kind": "port (self-consistency oracle, 1 thread)", "nonces": a.cpu_nonces, "solutions": cs,
+                                     "sol_per_s": cs / dt, "s_per_nonce": dt / a.cpu_nonces}
+            res["runs"].append(run)
+    print(json.dumps(res))
+
+
+if __name__ == "__main__":
+    main()
