@@ -10,12 +10,15 @@
 // bits, the last one cancelling two chunks at once; a solution is 2^k distinct indices whose tree satisfies
 // "left subtree's first index < right subtree's first index".
 //
-// GPU mapping: a round is (1) a scatter of the live rows into buckets by the top cbl-8 bits of the round's chunk
-// (one atomic slot counter per bucket, ~512 rows per bucket whatever (n,k) is, because N / 2^(cbl-8) = 512), then
-// (2) one CTA per bucket that counting-sorts its rows by the remaining 8 bits in shared memory and emits the XOR
-// of every colliding pair together with a two-slot back-reference.  Candidates of the last round are expanded,
-// canonically ordered and checked for distinct indices by one CTA each; an independent validator kernel recomputes
-// the BLAKE2b strings of a solution and re-checks every rule.
+// GPU mapping: rows LIVE in buckets.  Bucket b of round r holds the rows whose chunk r has top bits b
+// (cbl-8 of them, so a bucket's mean load is N / 2^(cbl-8) = 512 rows whatever (n,k) is); a row id is
+// bucket*slots + slot.  A round is ONE kernel, one CTA per bucket: the bucket's rows are copied into shared
+// memory (contiguous, coalesced), counting-sorted by the remaining 8 bits of the chunk, and every colliding pair
+// is XOR-ed and appended straight to the bucket its NEXT chunk selects (one atomic slot counter per bucket, so the
+// atomics are spread over thousands of addresses) together with a two-id back-reference.  The generator does the
+// same with the BLAKE2b strings, so there is no separate scatter pass.  Candidates of the last round are
+// expanded, canonically ordered and checked for distinct indices by one CTA each; an independent validator
+// kernel recomputes the BLAKE2b strings of a solution and re-checks every rule.
 #include "../../include/nx_equihash.h"
 #include "nx_blake2b.cuh"
 #include "nx_internal.hpp"
@@ -28,10 +31,8 @@ namespace nx
 namespace
 {
 constexpr int EQ_MAX_CHUNKS = 12;      // k+1
-constexpr int EQ_BUCKET_CAP = 2048;    // slots per bucket (mean load 512; tiny parameter sets have ONE bucket
-                                       // whose load swings widely, hence the generous headroom)
 constexpr int EQ_COLLIDE_THREADS = 256;
-constexpr int EQ_MAX_CANDIDATES = 4096;
+constexpr int EQ_MAX_CANDIDATES = 512;
 
 struct EqParams
 {
@@ -39,121 +40,154 @@ struct EqParams
     uint32_t N;
     int bucket_bits;      // cbl - 8 (0 when cbl == 8)
     uint32_t num_buckets;
+    uint32_t slots;       // row slots per bucket: 1024 (mean load 512); 2048 for tiny N, whose single bucket swings widely
 };
 
-__host__ __device__ inline uint32_t eq_chunk(const uint8_t* str, int cbl, int c)
+// Word-level BLAKE2b tail: the host has absorbed the header up to the last (partial) block; a thread appends its
+// 32-bit string counter at byte offset `fill` of that block and finalises.  No byte arrays, no local memory.
+struct EqMid
+{
+    uint64_t h[8];
+    uint64_t m[16];   // pending block as little-endian words, zero padded
+    uint64_t t;       // bytes absorbed before the pending block
+    uint32_t fill;    // bytes used in the pending block (multiple of 4, <= 124)
+};
+
+__device__ __forceinline__ void eq_digest_words(const EqMid& mid, uint32_t g, uint64_t out[8])
+{
+    uint64_t m[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) m[i] = mid.m[i];
+    const uint32_t w = mid.fill >> 3, sh = (mid.fill & 4u) * 8u;
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+        if ((uint32_t)i == w) m[i] |= (uint64_t)g << sh;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) out[i] = mid.h[i];
+    b2_compress(out, m, mid.t + mid.fill + 4, true);
+}
+
+// chunk c of string j of a digest held as words (big-endian bit order inside the byte string)
+__device__ __forceinline__ uint32_t eq_chunk_words(const uint64_t d[8], int byte0, int cbl, int c)
 {
     uint32_t v = 0;
+    const int bit0 = byte0 * 8 + c * cbl;
     for (int b = 0; b < cbl; ++b) {
-        const int bit = c * cbl + b;
-        v = (v << 1) | ((str[bit >> 3] >> (7 - (bit & 7))) & 1u);
+        const int bit = bit0 + b;
+        const uint32_t byte = (uint32_t)(d[bit >> 6] >> (8 * ((bit >> 3) & 7))) & 0xffu;
+        v = (v << 1) | ((byte >> (7 - (bit & 7))) & 1u);
     }
     return v;
 }
 
-// chunks of initial string i (shared by the generator and the validator)
-__device__ void eq_string_chunks(const EqParams& p, const Blake2bState& mid, uint32_t i, uint32_t* out)
+// chunks of initial string i (used by the validator)
+__device__ void eq_string_chunks(const EqParams& p, const EqMid& mid, uint32_t i, uint32_t* out)
 {
-    Blake2bState s = mid;
-    const uint32_t g = i / (uint32_t)p.ipp;
-    uint8_t le[4] = {(uint8_t)g, (uint8_t)(g >> 8), (uint8_t)(g >> 16), (uint8_t)(g >> 24)};
-    b2_update(s, le, 4);
-    uint8_t digest[64];
-    b2_final(s, digest);
-    const uint8_t* str = digest + (i % (uint32_t)p.ipp) * p.hash_bytes;
-    for (int c = 0; c < p.chunks; ++c) out[c] = eq_chunk(str, p.cbl, c);
+    uint64_t d[8];
+    eq_digest_words(mid, i / (uint32_t)p.ipp, d);
+    const int byte0 = (int)(i % (uint32_t)p.ipp) * p.hash_bytes;
+    for (int c = 0; c < p.chunks; ++c) out[c] = eq_chunk_words(d, byte0, p.cbl, c);
 }
 
-// ---- round 0: N strings -> rows[i][chunks] ----
-__global__ void eq_generate_kernel(EqParams p, Blake2bState mid, uint32_t* __restrict__ rows)
+// ---- round 0: N strings, each appended to the bucket its chunk 0 selects ----
+__global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__ rows, uint32_t* __restrict__ leaf,
+                                   uint32_t* __restrict__ bucket_cnt)
 {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;  // one digest per thread
     if (g >= (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp) return;  // N need not be a multiple of 512/n
-    Blake2bState s = mid;
-    uint8_t le[4] = {(uint8_t)g, (uint8_t)(g >> 8), (uint8_t)(g >> 16), (uint8_t)(g >> 24)};
-    b2_update(s, le, 4);
-    uint8_t digest[64];
-    b2_final(s, digest);
+    uint64_t d[8];
+    eq_digest_words(mid, g, d);
     for (int j = 0; j < p.ipp; ++j) {
         const uint32_t i = g * (uint32_t)p.ipp + (uint32_t)j;
         if (i >= p.N) break;
-        const uint8_t* str = digest + j * p.hash_bytes;
-        for (int c = 0; c < p.chunks; ++c) rows[(size_t)i * p.chunks + c] = eq_chunk(str, p.cbl, c);
-    }
-}
-
-// ---- scatter live rows into buckets by the top bits of chunk r ----
-__global__ void eq_scatter_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ count_ptr,
-                                  uint32_t count_cap, uint32_t* __restrict__ bucket_cnt, uint32_t* __restrict__ bucket_rows)
-{
-    const uint32_t count = min(*count_ptr, count_cap);
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const uint32_t c = rows[(size_t)i * p.chunks + r];
-        const uint32_t b = p.bucket_bits ? (c >> 8) : 0u;
+        uint32_t ch[EQ_MAX_CHUNKS];
+        for (int c = 0; c < p.chunks; ++c) ch[c] = eq_chunk_words(d, j * p.hash_bytes, p.cbl, c);
+        const uint32_t b = p.bucket_bits ? (ch[0] >> 8) : 0u;
         const uint32_t slot = atomicAdd(&bucket_cnt[b], 1u);
-        if (slot < EQ_BUCKET_CAP) bucket_rows[(size_t)b * EQ_BUCKET_CAP + slot] = i;
+        if (slot >= p.slots) continue;
+        const uint32_t id = b * p.slots + slot;
+        for (int c = 0; c < p.chunks; ++c) rows[(size_t)id * p.chunks + c] = ch[c];
+        leaf[id] = i;
     }
 }
 
-// ---- one CTA per bucket: counting sort on the low 8 bits in shared memory, emit every colliding pair ----
+// ---- one round: one CTA per bucket ----
+// dynamic shared memory: [rows of the bucket: slots x chunks words][order: slots x u16][key: slots x u16]
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS)
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ bucket_cnt,
-                  const uint32_t* __restrict__ bucket_rows, uint32_t* __restrict__ next_rows, uint2* __restrict__ tree,
-                  uint32_t* __restrict__ out_count, uint32_t out_cap)
+                  uint32_t* __restrict__ next_rows, uint32_t* __restrict__ next_cnt, uint2* __restrict__ tree,
+                  uint32_t* __restrict__ cand_count)
 {
-    __shared__ uint32_t ids[EQ_BUCKET_CAP];
-    __shared__ uint32_t sorted[EQ_BUCKET_CAP];
-    __shared__ uint16_t keys[EQ_BUCKET_CAP];
-    __shared__ uint32_t hist[257];
+    extern __shared__ uint32_t eq_smem[];
+    __shared__ uint32_t hist[256];
     __shared__ uint32_t start[257];
-    const uint32_t b = blockIdx.x;
-    const uint32_t cnt = min(bucket_cnt[b], (uint32_t)EQ_BUCKET_CAP);
+    __shared__ uint32_t warp_sum[EQ_COLLIDE_THREADS / 32];
+    const uint32_t C = (uint32_t)p.chunks;
+    uint32_t* const rs = eq_smem;
+    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * C);
+    uint16_t* const key = order + p.slots;
+    const uint32_t b = blockIdx.x, t = threadIdx.x;
+    const uint32_t cnt = min(bucket_cnt[b], p.slots);
     const bool last = r == p.k - 1;
-    for (uint32_t i = threadIdx.x; i < 257; i += EQ_COLLIDE_THREADS) hist[i] = 0;
+    const uint32_t base = b * p.slots;
+
+    hist[t] = 0;
+    const uint32_t* src = rows + (size_t)base * C;
+    for (uint32_t i = t; i < cnt * C; i += EQ_COLLIDE_THREADS) rs[i] = src[i];  // contiguous: the bucket's rows
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < cnt; i += EQ_COLLIDE_THREADS) {
-        const uint32_t id = bucket_rows[(size_t)b * EQ_BUCKET_CAP + i];
-        const uint32_t key = rows[(size_t)id * p.chunks + r] & 0xffu;
-        ids[i] = id;
-        keys[i] = (uint16_t)key;
-        atomicAdd(&hist[key], 1u);
+    for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
+        const uint32_t kk = rs[i * C + r] & 0xffu;
+        key[i] = (uint16_t)kk;
+        atomicAdd(&hist[kk], 1u);
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t acc = 0;
-        for (int i = 0; i < 256; ++i) {
-            start[i] = acc;
-            acc += hist[i];
+    {   // exclusive scan of the 256 bins: thread t owns bin t
+        const uint32_t v = hist[t];
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+            if ((t & 31u) >= (uint32_t)o) inc += u;
         }
-        start[256] = acc;
+        if ((t & 31u) == 31u) warp_sum[t >> 5] = inc;
+        __syncthreads();
+        uint32_t off = 0;
+        for (uint32_t w = 0; w < (t >> 5); ++w) off += warp_sum[w];
+        start[t] = off + inc - v;
+        if (t == EQ_COLLIDE_THREADS - 1) start[256] = off + inc;
+        __syncthreads();
+        hist[t] = start[t];  // running insert positions
     }
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < 256; i += EQ_COLLIDE_THREADS) hist[i] = start[i];  // running insert positions
+    for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) order[atomicAdd(&hist[key[i]], 1u)] = (uint16_t)i;
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < cnt; i += EQ_COLLIDE_THREADS) sorted[atomicAdd(&hist[keys[i]], 1u)] = ids[i];
-    __syncthreads();
-    // position i pairs with every later position of its key group
-    for (uint32_t i = threadIdx.x; i < cnt; i += EQ_COLLIDE_THREADS) {
-        const uint32_t ia = sorted[i];
-        const uint32_t key = rows[(size_t)ia * p.chunks + r] & 0xffu;
-        const uint32_t end = start[key + 1];
-        const uint32_t* ra = rows + (size_t)ia * p.chunks;
+    // sorted position i pairs with every later position of its key group
+    for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
+        const uint32_t sa = order[i];
+        const uint32_t end = start[key[sa] + 1u];
+        const uint32_t* ra = rs + sa * C;
         for (uint32_t j = i + 1; j < end; ++j) {
-            const uint32_t ib = sorted[j];
-            const uint32_t* rb = rows + (size_t)ib * p.chunks;
+            const uint32_t sb = order[j];
+            const uint32_t* rb = rs + sb * C;
             uint32_t x[EQ_MAX_CHUNKS];
             uint32_t any = 0;
-            for (int c = r + 1; c < p.chunks; ++c) {
+            for (uint32_t c = (uint32_t)r + 1; c < C; ++c) {
                 x[c] = ra[c] ^ rb[c];
                 any |= x[c];
             }
-            if (last ? any != 0 : any == 0) continue;  // last round: both remaining chunks must cancel; earlier: drop
-                                                       // identical remainders (the subtrees share their index set)
-            const uint32_t slot = atomicAdd(out_count, 1u);
-            if (slot >= out_cap) continue;
-            tree[slot] = make_uint2(ia, ib);
-            if (!last)
-                for (int c = 0; c < p.chunks; ++c) next_rows[(size_t)slot * p.chunks + c] = c <= r ? 0u : x[c];
+            if (last) {
+                if (any != 0) continue;  // the last round must cancel both remaining chunks
+                const uint32_t slot = atomicAdd(cand_count, 1u);
+                if (slot < EQ_MAX_CANDIDATES) tree[slot] = make_uint2(base + sa, base + sb);
+            } else {
+                if (any == 0) continue;  // identical remainders: the two subtrees share their index set
+                const uint32_t nb = p.bucket_bits ? (x[r + 1] >> 8) : 0u;
+                const uint32_t slot = atomicAdd(&next_cnt[nb], 1u);
+                if (slot >= p.slots) continue;
+                const uint32_t id = nb * p.slots + slot;
+                for (uint32_t c = (uint32_t)r + 1; c < C; ++c) next_rows[(size_t)id * C + c] = x[c];
+                tree[id] = make_uint2(base + sa, base + sb);
+            }
         }
     }
 }
@@ -163,6 +197,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
 struct EqTrees
 {
     const uint2* t[EQ_MAX_CHUNKS];
+    const uint32_t* leaf;  // row id of round 0 -> initial string index
 };
 
 __global__ void eq_recover_kernel(EqParams p, EqTrees trees, const uint32_t* __restrict__ cand_count, uint32_t cand_cap,
@@ -182,7 +217,7 @@ __global__ void eq_recover_kernel(EqParams p, EqTrees trees, const uint32_t* __r
         const uint2 pr = trees.t[round][slot];
         slot = ((t >> (round - 1)) & 1u) ? pr.y : pr.x;
     }
-    idx[t] = slot;  // a round-0 slot IS the initial index
+    idx[t] = trees.leaf[slot];  // round-0 row id -> initial string index
     __syncthreads();
     // ordering rule, bottom-up: at every node the subtree with the smaller first index goes left
     for (int level = 0; level < p.k; ++level) {
@@ -208,7 +243,7 @@ __global__ void eq_recover_kernel(EqParams p, EqTrees trees, const uint32_t* __r
 
 // ---- GPU-side validator: recompute the strings of a claimed solution and re-check every rule ----
 // grid = solutions, block = 2^k threads.  rows live in dynamic shared memory: leaves * chunks words.
-__global__ void eq_validate_kernel(EqParams p, Blake2bState mid, const uint32_t* __restrict__ indices, uint32_t* __restrict__ verdict)
+__global__ void eq_validate_kernel(EqParams p, EqMid mid, const uint32_t* __restrict__ indices, uint32_t* __restrict__ verdict)
 {
     extern __shared__ uint32_t vrows[];
     __shared__ uint32_t vidx[512];
@@ -266,18 +301,40 @@ bool eq_make_params(EqParams& p, int n, int k)
     p.N = 1u << (cbl + 1);
     p.bucket_bits = cbl - 8;
     p.num_buckets = 1u << p.bucket_bits;
+    p.slots = p.N <= (1u << 12) ? 2048u : 1024u;
     return true;
 }
 
-void eq_midstate(const EqParams& p, const uint8_t tag[8], const uint8_t* header, size_t len, Blake2bState& s)
+// Absorb the header on the host up to its last partial block.  The string counter is appended on the device as one
+// aligned 32-bit store, so the header length must be a multiple of 4 (every real header is).
+bool eq_midstate(const EqParams& p, const uint8_t tag[8], const uint8_t* header, size_t len, EqMid& mid)
 {
+    if (len % 4 != 0) return false;
     uint8_t personal[16];
     std::memcpy(personal, tag, 8);
     const uint32_t le_n = (uint32_t)p.n, le_k = (uint32_t)p.k;
     std::memcpy(personal + 8, &le_n, 4);
     std::memcpy(personal + 12, &le_k, 4);
+    Blake2bState s;
     b2_init(s, (uint32_t)p.digest_bytes, personal);
     b2_update(s, header, len);
+    // b2_update leaves the last block pending even when it is full; 4 more bytes will follow, so a full one is
+    // compressed here and the counter starts a fresh block (len % 4 == 0 means a partial block has >= 4 free bytes)
+    if (s.buflen == 128) {
+        uint64_t m[16];
+        b2_load_block(s.buf, m);
+        s.t += 128;
+        b2_compress(s.h, m, s.t, false);
+        s.buflen = 0;
+        std::memset(s.buf, 0, 128);
+    }
+    for (int i = 0; i < 8; ++i) mid.h[i] = s.h[i];
+    uint8_t block[128] = {0};
+    std::memcpy(block, s.buf, s.buflen);
+    b2_load_block(block, mid.m);
+    mid.t = s.t;
+    mid.fill = s.buflen;
+    return true;
 }
 }  // namespace
 }  // namespace nx
@@ -289,13 +346,13 @@ struct nx_equihash
     EqParams p;
     int device;
     uint8_t tag[8];
-    uint32_t cap;  // rows per round
-    uint32_t* rows[2] = {nullptr, nullptr};
-    uint32_t* bucket_cnt = nullptr;
-    uint32_t* bucket_rows = nullptr;
-    uint2* tree[EQ_MAX_CHUNKS] = {nullptr};
-    uint32_t* counts = nullptr;       // [k+1] row counts per round (device)
-    uint32_t* cand_indices = nullptr; // EQ_MAX_CANDIDATES x 2^k
+    size_t smem_bytes = 0;            // dynamic shared memory of eq_collide_kernel
+    uint32_t* rows[2] = {nullptr, nullptr};     // num_buckets x slots x chunks words, ping-pong
+    uint32_t* bucket_cnt[2] = {nullptr, nullptr};
+    uint32_t* leaf = nullptr;                   // round-0 row id -> initial string index
+    uint2* tree[EQ_MAX_CHUNKS] = {nullptr};     // tree[r], r = 1..k: pairs that made the rows of round r
+    uint32_t* cand_count = nullptr;
+    uint32_t* cand_indices = nullptr;           // EQ_MAX_CANDIDATES x 2^k
     uint32_t* cand_valid = nullptr;
     uint32_t* verdict = nullptr;
     cudaStream_t stream = nullptr;
@@ -319,13 +376,14 @@ void nx_equihash_destroy(nx_equihash* s)
     if (!s) return;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < 2; ++i) {
         if (s->rows[i]) cudaFree(s->rows[i]);
-    if (s->bucket_cnt) cudaFree(s->bucket_cnt);
-    if (s->bucket_rows) cudaFree(s->bucket_rows);
+        if (s->bucket_cnt[i]) cudaFree(s->bucket_cnt[i]);
+    }
+    if (s->leaf) cudaFree(s->leaf);
     for (int i = 0; i < EQ_MAX_CHUNKS; ++i)
         if (s->tree[i]) cudaFree(s->tree[i]);
-    if (s->counts) cudaFree(s->counts);
+    if (s->cand_count) cudaFree(s->cand_count);
     if (s->cand_indices) cudaFree(s->cand_indices);
     if (s->cand_valid) cudaFree(s->cand_valid);
     if (s->verdict) cudaFree(s->verdict);
@@ -363,23 +421,25 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     s->p = p;
     s->device = device;
     std::memcpy(s->tag, tag, 8);
-    // rows per round hover around N (count' ~ count^2 / N); relative swings are large only for tiny N
-    s->cap = p.N <= (1u << 12) ? 4 * p.N : p.N + p.N / 2;
-    const size_t row_bytes = (size_t)s->cap * p.chunks * 4;
+    const size_t ids = (size_t)p.num_buckets * p.slots;  // row ids per round
+    const size_t row_bytes = ids * p.chunks * 4;
     const uint32_t leaves = 1u << k;
+    s->smem_bytes = (size_t)p.slots * p.chunks * 4 + (size_t)p.slots * 2 * 2;
     bool ok = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) == cudaSuccess && cudaEventCreate(&s->ev0) == cudaSuccess &&
               cudaEventCreate(&s->ev1) == cudaSuccess && cudaMalloc((void**)&s->rows[0], row_bytes) == cudaSuccess &&
               cudaMalloc((void**)&s->rows[1], row_bytes) == cudaSuccess &&
-              cudaMalloc((void**)&s->bucket_cnt, (size_t)p.num_buckets * 4) == cudaSuccess &&
-              cudaMalloc((void**)&s->bucket_rows, (size_t)p.num_buckets * EQ_BUCKET_CAP * 4) == cudaSuccess &&
-              cudaMalloc((void**)&s->counts, (size_t)(k + 2) * 4) == cudaSuccess &&
+              cudaMalloc((void**)&s->bucket_cnt[0], (size_t)p.num_buckets * 4) == cudaSuccess &&
+              cudaMalloc((void**)&s->bucket_cnt[1], (size_t)p.num_buckets * 4) == cudaSuccess &&
+              cudaMalloc((void**)&s->leaf, ids * 4) == cudaSuccess && cudaMalloc((void**)&s->cand_count, 4) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_indices, (size_t)EQ_MAX_CANDIDATES * leaves * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_valid, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->verdict, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess;
     for (int r = 1; ok && r <= k; ++r)
-        ok = cudaMalloc((void**)&s->tree[r], (size_t)(r == k ? EQ_MAX_CANDIDATES : s->cap) * sizeof(uint2)) == cudaSuccess;
+        ok = cudaMalloc((void**)&s->tree[r], (r == k ? (size_t)EQ_MAX_CANDIDATES : ids) * sizeof(uint2)) == cudaSuccess;
+    if (ok && s->smem_bytes > 48 * 1024)
+        ok = cudaFuncSetAttribute(eq_collide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_bytes) == cudaSuccess;
     if (!ok) {
-        set_error("Equihash(%d,%d): device allocation failed: %s", n, k, cudaGetErrorString(cudaGetLastError()));
+        set_error("Equihash(%d,%d): device set-up failed: %s", n, k, cudaGetErrorString(cudaGetLastError()));
         nx_equihash_destroy(s);
         return NX_ERR_OOM;
     }
@@ -387,8 +447,9 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     return NX_OK;
 }
 
-// All solutions of one header (header = everything that is hashed before the LE32 string counter, nonce included).
-// solutions_out receives up to max_solutions minimal encodings, sorted bytewise; *n_solutions the number found.
+// All solutions of one header (header = everything that is hashed before the LE32 string counter, nonce included;
+// its length must be a multiple of 4).  solutions_out receives up to max_solutions minimal encodings, sorted
+// bytewise; *n_solutions the number found.
 int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, uint8_t* solutions_out, int max_solutions,
                       int* n_solutions)
 {
@@ -400,42 +461,43 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     std::lock_guard<std::mutex> lk(s->mu);
     NX_CUDA(cudaSetDevice(s->device));
     const EqParams& p = s->p;
-    Blake2bState mid;
-    eq_midstate(p, s->tag, header, header_len, mid);
+    EqMid mid;
+    if (!eq_midstate(p, s->tag, header, header_len, mid)) {
+        set_error("Equihash header length %zu is not a multiple of 4", header_len);
+        return NX_ERR_INVALID;
+    }
     const int k = p.k;
     int launches = 0;
+    const size_t cnt_bytes = (size_t)p.num_buckets * 4;
 
     NX_CUDA(cudaEventRecord(s->ev0, s->stream));
-    NX_CUDA(cudaMemsetAsync(s->counts, 0, (size_t)(k + 2) * 4, s->stream));
+    NX_CUDA(cudaMemsetAsync(s->cand_count, 0, 4, s->stream));
+    NX_CUDA(cudaMemsetAsync(s->bucket_cnt[0], 0, cnt_bytes, s->stream));
     const uint32_t digests = (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp;
-    eq_generate_kernel<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0]);
+    eq_generate_kernel<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0], s->leaf, s->bucket_cnt[0]);
     ++launches;
-    NX_CUDA(cudaMemcpyAsync(s->counts, &p.N, 4, cudaMemcpyHostToDevice, s->stream));  // p lives in *s: stays valid
     for (int r = 0; r < k; ++r) {
-        const bool last = r == k - 1;
-        const uint32_t* in = s->rows[r & 1];
-        uint32_t* outr = s->rows[(r + 1) & 1];
-        NX_CUDA(cudaMemsetAsync(s->bucket_cnt, 0, (size_t)p.num_buckets * 4, s->stream));
-        eq_scatter_kernel<<<148 * 8, 256, 0, s->stream>>>(p, r, in, s->counts + r, s->cap, s->bucket_cnt, s->bucket_rows);
-        eq_collide_kernel<<<p.num_buckets, EQ_COLLIDE_THREADS, 0, s->stream>>>(
-            p, r, in, s->bucket_cnt, s->bucket_rows, outr, s->tree[r + 1], s->counts + r + 1,
-            last ? (uint32_t)EQ_MAX_CANDIDATES : s->cap);
-        launches += 2;
+        NX_CUDA(cudaMemsetAsync(s->bucket_cnt[(r + 1) & 1], 0, cnt_bytes, s->stream));
+        eq_collide_kernel<<<p.num_buckets, EQ_COLLIDE_THREADS, s->smem_bytes, s->stream>>>(
+            p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
+            s->cand_count);
+        ++launches;
     }
     EqTrees trees;
     for (int i = 0; i < EQ_MAX_CHUNKS; ++i) trees.t[i] = s->tree[i];
+    trees.leaf = s->leaf;
     const uint32_t leaves = 1u << k;
-    eq_recover_kernel<<<EQ_MAX_CANDIDATES, leaves, 0, s->stream>>>(p, trees, s->counts + k, EQ_MAX_CANDIDATES, s->cand_indices,
+    eq_recover_kernel<<<EQ_MAX_CANDIDATES, leaves, 0, s->stream>>>(p, trees, s->cand_count, EQ_MAX_CANDIDATES, s->cand_indices,
                                                                    s->cand_valid);
     ++launches;
     NX_CUDA(cudaGetLastError());
     NX_CUDA(cudaEventRecord(s->ev1, s->stream));
-    std::vector<uint32_t> counts((size_t)k + 2);
-    NX_CUDA(cudaMemcpyAsync(counts.data(), s->counts, (size_t)(k + 2) * 4, cudaMemcpyDeviceToHost, s->stream));
+    uint32_t ncand = 0;
+    NX_CUDA(cudaMemcpyAsync(&ncand, s->cand_count, 4, cudaMemcpyDeviceToHost, s->stream));
     NX_CUDA(cudaStreamSynchronize(s->stream));
     NX_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
     s->last_launches = launches;
-    const uint32_t ncand = std::min<uint32_t>(counts[(size_t)k], EQ_MAX_CANDIDATES);
+    ncand = std::min<uint32_t>(ncand, EQ_MAX_CANDIDATES);
     if (ncand == 0) return NX_OK;
     std::vector<uint32_t> valid(ncand), idx((size_t)ncand * leaves);
     NX_CUDA(cudaMemcpy(valid.data(), s->cand_valid, (size_t)ncand * 4, cudaMemcpyDeviceToHost));
@@ -486,8 +548,11 @@ int nx_equihash_validate(nx_equihash* s, const uint8_t* header, size_t header_le
             idx[(size_t)c * leaves + i] = v;
         }
     }
-    Blake2bState mid;
-    eq_midstate(p, s->tag, header, header_len, mid);
+    EqMid mid;
+    if (!eq_midstate(p, s->tag, header, header_len, mid)) {
+        set_error("Equihash header length %zu is not a multiple of 4", header_len);
+        return NX_ERR_INVALID;
+    }
     NX_CUDA(cudaMemcpyAsync(s->cand_indices, idx.data(), idx.size() * 4, cudaMemcpyHostToDevice, s->stream));
     eq_validate_kernel<<<count, leaves, (size_t)leaves * p.chunks * 4, s->stream>>>(p, mid, s->cand_indices, s->verdict);
     NX_CUDA(cudaGetLastError());
