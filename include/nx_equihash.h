@@ -39,6 +39,12 @@ int nx_equihash_solve(nx_equihash* solver, const uint8_t* header, size_t header_
 int nx_equihash_validate(nx_equihash* solver, const uint8_t* header, size_t header_len, const uint8_t* solutions,
                          int count, uint8_t* verdict);
 
+/* Rows or candidates that did not fit their bucket during the last solve and were lost (each bucket has twice its
+ * mean load in slots, so this is 0 in normal operation; a non-zero value means solutions may have been missed). */
+int nx_equihash_last_dropped(const nx_equihash* solver);
+/* Final-round candidates of the last solve (valid solutions plus trees that repeat an index). */
+int nx_equihash_last_candidates(const nx_equihash* solver);
+
 /* Device time (CUDA events on the solver's stream) and kernel launches of the last nx_equihash_solve. */
 int nx_equihash_last_timing(const nx_equihash* solver, float* kernel_ms, int* launches);
 

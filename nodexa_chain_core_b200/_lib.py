@@ -133,6 +133,8 @@ def _load() -> C.CDLL:
         "nx_equihash_destroy": (None, [vp]),
         "nx_equihash_solve": (i, [vp, u8p, sz, u8p, i, C.POINTER(i)]),
         "nx_equihash_validate": (i, [vp, u8p, sz, u8p, i, u8p]),
+        "nx_equihash_last_dropped": (i, [vp]),
+        "nx_equihash_last_candidates": (i, [vp]),
         "nx_equihash_last_timing": (i, [vp, C.POINTER(C.c_float), C.POINTER(i)]),
         # introspection (nx_tools.cpp; not part of the drop-in surface)
         "nx_kawpow_program_source": (sz, [u64, u32, i, C.c_char_p, sz]),

@@ -32,7 +32,7 @@ namespace
 {
 constexpr int EQ_MAX_CHUNKS = 12;      // k+1
 constexpr int EQ_COLLIDE_THREADS = 256;
-constexpr int EQ_MAX_CANDIDATES = 512;
+constexpr int EQ_MAX_CANDIDATES = 8192;
 
 struct EqParams
 {
@@ -91,7 +91,7 @@ __device__ void eq_string_chunks(const EqParams& p, const EqMid& mid, uint32_t i
 
 // ---- round 0: N strings, each appended to the bucket its chunk 0 selects ----
 __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__ rows, uint32_t* __restrict__ leaf,
-                                   uint32_t* __restrict__ bucket_cnt)
+                                   uint32_t* __restrict__ bucket_cnt, uint32_t* __restrict__ dropped)
 {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;  // one digest per thread
     if (g >= (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp) return;  // N need not be a multiple of 512/n
@@ -104,7 +104,10 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
         for (int c = 0; c < p.chunks; ++c) ch[c] = eq_chunk_words(d, j * p.hash_bytes, p.cbl, c);
         const uint32_t b = p.bucket_bits ? (ch[0] >> 8) : 0u;
         const uint32_t slot = atomicAdd(&bucket_cnt[b], 1u);
-        if (slot >= p.slots) continue;
+        if (slot >= p.slots) {
+            atomicAdd(dropped, 1u);
+            continue;
+        }
         const uint32_t id = b * p.slots + slot;
         for (int c = 0; c < p.chunks; ++c) rows[(size_t)id * p.chunks + c] = ch[c];
         leaf[id] = i;
@@ -116,7 +119,7 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS)
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ bucket_cnt,
                   uint32_t* __restrict__ next_rows, uint32_t* __restrict__ next_cnt, uint2* __restrict__ tree,
-                  uint32_t* __restrict__ cand_count)
+                  const uint2* __restrict__ prev_tree, uint32_t* __restrict__ cand_count)
 {
     extern __shared__ uint32_t eq_smem[];
     __shared__ uint32_t hist[256];
@@ -130,6 +133,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     const uint32_t cnt = min(bucket_cnt[b], p.slots);
     const bool last = r == p.k - 1;
     const uint32_t base = b * p.slots;
+    if (cnt == 0) return;
 
     hist[t] = 0;
     const uint32_t* src = rows + (size_t)base * C;
@@ -177,13 +181,20 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
             }
             if (last) {
                 if (any != 0) continue;  // the last round must cancel both remaining chunks
+                if (prev_tree) {         // cheap early filter: two rows that share a child share indices
+                    const uint2 pa = prev_tree[base + sa], pb = prev_tree[base + sb];
+                    if (pa.x == pb.x || pa.x == pb.y || pa.y == pb.x || pa.y == pb.y) continue;
+                }
                 const uint32_t slot = atomicAdd(cand_count, 1u);
                 if (slot < EQ_MAX_CANDIDATES) tree[slot] = make_uint2(base + sa, base + sb);
             } else {
                 if (any == 0) continue;  // identical remainders: the two subtrees share their index set
                 const uint32_t nb = p.bucket_bits ? (x[r + 1] >> 8) : 0u;
                 const uint32_t slot = atomicAdd(&next_cnt[nb], 1u);
-                if (slot >= p.slots) continue;
+                if (slot >= p.slots) {
+                    atomicAdd(cand_count + 1, 1u);  // a row that did not fit its bucket is lost: counted, reported
+                    continue;
+                }
                 const uint32_t id = nb * p.slots + slot;
                 for (uint32_t c = (uint32_t)r + 1; c < C; ++c) next_rows[(size_t)id * C + c] = x[c];
                 tree[id] = make_uint2(base + sa, base + sb);
@@ -359,6 +370,8 @@ struct nx_equihash
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0;
     int last_launches = 0;
+    uint32_t last_candidates = 0;
+    uint32_t last_dropped = 0;  // rows/candidates lost to a full bucket in the last solve (0 in normal operation)
     std::mutex mu;
 };
 
@@ -430,7 +443,7 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
               cudaMalloc((void**)&s->rows[1], row_bytes) == cudaSuccess &&
               cudaMalloc((void**)&s->bucket_cnt[0], (size_t)p.num_buckets * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->bucket_cnt[1], (size_t)p.num_buckets * 4) == cudaSuccess &&
-              cudaMalloc((void**)&s->leaf, ids * 4) == cudaSuccess && cudaMalloc((void**)&s->cand_count, 4) == cudaSuccess &&
+              cudaMalloc((void**)&s->leaf, ids * 4) == cudaSuccess && cudaMalloc((void**)&s->cand_count, 8) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_indices, (size_t)EQ_MAX_CANDIDATES * leaves * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_valid, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->verdict, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess;
@@ -471,33 +484,37 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     const size_t cnt_bytes = (size_t)p.num_buckets * 4;
 
     NX_CUDA(cudaEventRecord(s->ev0, s->stream));
-    NX_CUDA(cudaMemsetAsync(s->cand_count, 0, 4, s->stream));
+    NX_CUDA(cudaMemsetAsync(s->cand_count, 0, 8, s->stream));
     NX_CUDA(cudaMemsetAsync(s->bucket_cnt[0], 0, cnt_bytes, s->stream));
     const uint32_t digests = (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp;
-    eq_generate_kernel<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0], s->leaf, s->bucket_cnt[0]);
+    eq_generate_kernel<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0], s->leaf, s->bucket_cnt[0], s->cand_count + 1);
     ++launches;
     for (int r = 0; r < k; ++r) {
         NX_CUDA(cudaMemsetAsync(s->bucket_cnt[(r + 1) & 1], 0, cnt_bytes, s->stream));
         eq_collide_kernel<<<p.num_buckets, EQ_COLLIDE_THREADS, s->smem_bytes, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
-            s->cand_count);
+            r >= 1 ? s->tree[r] : nullptr, s->cand_count);
         ++launches;
     }
-    EqTrees trees;
-    for (int i = 0; i < EQ_MAX_CHUNKS; ++i) trees.t[i] = s->tree[i];
-    trees.leaf = s->leaf;
+    uint32_t stats[2] = {0, 0};
+    NX_CUDA(cudaMemcpyAsync(stats, s->cand_count, 8, cudaMemcpyDeviceToHost, s->stream));
+    NX_CUDA(cudaStreamSynchronize(s->stream));
+    s->last_dropped = stats[1] + (stats[0] > EQ_MAX_CANDIDATES ? stats[0] - EQ_MAX_CANDIDATES : 0);
+    const uint32_t ncand = std::min<uint32_t>(stats[0], EQ_MAX_CANDIDATES);
     const uint32_t leaves = 1u << k;
-    eq_recover_kernel<<<EQ_MAX_CANDIDATES, leaves, 0, s->stream>>>(p, trees, s->cand_count, EQ_MAX_CANDIDATES, s->cand_indices,
-                                                                   s->cand_valid);
-    ++launches;
-    NX_CUDA(cudaGetLastError());
+    if (ncand) {
+        EqTrees trees;
+        for (int i = 0; i < EQ_MAX_CHUNKS; ++i) trees.t[i] = s->tree[i];
+        trees.leaf = s->leaf;
+        eq_recover_kernel<<<ncand, leaves, 0, s->stream>>>(p, trees, s->cand_count, EQ_MAX_CANDIDATES, s->cand_indices, s->cand_valid);
+        ++launches;
+        NX_CUDA(cudaGetLastError());
+    }
     NX_CUDA(cudaEventRecord(s->ev1, s->stream));
-    uint32_t ncand = 0;
-    NX_CUDA(cudaMemcpyAsync(&ncand, s->cand_count, 4, cudaMemcpyDeviceToHost, s->stream));
     NX_CUDA(cudaStreamSynchronize(s->stream));
     NX_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
     s->last_launches = launches;
-    ncand = std::min<uint32_t>(ncand, EQ_MAX_CANDIDATES);
+    s->last_candidates = ncand;
     if (ncand == 0) return NX_OK;
     std::vector<uint32_t> valid(ncand), idx((size_t)ncand * leaves);
     NX_CUDA(cudaMemcpy(valid.data(), s->cand_valid, (size_t)ncand * 4, cudaMemcpyDeviceToHost));
@@ -562,6 +579,9 @@ int nx_equihash_validate(nx_equihash* s, const uint8_t* header, size_t header_le
     for (int c = 0; c < count; ++c) verdict[c] = (uint8_t)(v[(size_t)c] ? 1 : 0);
     return NX_OK;
 }
+
+int nx_equihash_last_dropped(const nx_equihash* s) { return s ? (int)s->last_dropped : 0; }
+int nx_equihash_last_candidates(const nx_equihash* s) { return s ? (int)s->last_candidates : 0; }
 
 int nx_equihash_last_timing(const nx_equihash* s, float* kernel_ms, int* launches)
 {

@@ -34,6 +34,14 @@ class Solver:
         check(lib.nx_equihash_validate(self._h, inb(header), len(header), inb(b"".join(solutions)), len(solutions), v))
         return [bool(v[i]) for i in range(len(solutions))]
 
+    @property
+    def last_dropped(self) -> int:
+        return lib.nx_equihash_last_dropped(self._h)
+
+    @property
+    def last_candidates(self) -> int:
+        return lib.nx_equihash_last_candidates(self._h)
+
     def last_timing(self):
         ms, n = C.c_float(), C.c_int()
         lib.nx_equihash_last_timing(self._h, C.byref(ms), C.byref(n))

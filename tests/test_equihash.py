@@ -60,6 +60,7 @@ def test_gpu_solution_set_equals_cpu_oracle(nx, gpu, oracle, n, k, nonces):
             got = s.solve(hdr)
             want = oracle.equihash_solve(n, k, TAG, hdr)
             assert got == want, (n, k, nonce, len(got), len(want))
+            assert s.last_dropped == 0
             assert s.validate(hdr, got) == [True] * len(got)
             found += len(got)
     assert found > 0 or n == 48
@@ -91,7 +92,7 @@ def test_gpu_full_sized_parameters_validate(nx, gpu, oracle, n, k):
                 assert s.validate(_header(nonce + 50), [sols[0]]) == [False]
                 assert not oracle.equihash_validate(n, k, TAG, hdr, bytes(enc))
         ms, launches = s.last_timing()
-        assert ms > 0 and launches == 2 + 2 * k
+        assert ms > 0 and launches in (1 + k, 2 + k)
     assert total >= 4  # ~1.9 solutions per nonce are expected
 
 

@@ -31,16 +31,18 @@ def main():
         with nx.equihash.Solver(n, k, TAG) as s:
             for w in range(3):
                 s.solve(header(10**6 + w))
-            sols, kernel_ms = 0, 0.0
+            sols, kernel_ms, dropped, cands = 0, 0.0, 0, 0
             t0 = time.perf_counter()
             for i in range(a.nonces):
                 got = s.solve(header(i))
                 sols += len(got)
                 kernel_ms += s.last_timing()[0]
+                dropped += s.last_dropped
+                cands += s.last_candidates
             wall = time.perf_counter() - t0
             run = {"n": n, "k": k, "nonces": a.nonces, "solutions": sols, "sol_per_s_device": sols / (kernel_ms * 1e-3),
                    "sol_per_s_e2e": sols / wall, "ms_per_nonce_device": kernel_ms / a.nonces, "ms_per_nonce_e2e": wall / a.nonces * 1e3,
-                   "launches_per_nonce": s.last_timing()[1]}
+                   "launches_per_nonce": s.last_timing()[1], "rows_dropped": dropped, "candidates": cands}
             if (n, k) == (200, 9) and a.cpu_nonces:
                 t0 = time.perf_counter()
                 cs = sum(len(orc.equihash_solve(n, k, TAG, header(i))) for i in range(a.cpu_nonces))
