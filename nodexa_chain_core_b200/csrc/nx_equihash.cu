@@ -67,17 +67,22 @@ __device__ __forceinline__ void eq_digest_words(const EqMid& mid, uint32_t g, ui
     b2_compress(out, m, mid.t + mid.fill + 4, true);
 }
 
-// chunk c of string j of a digest held as words (big-endian bit order inside the byte string)
+// chunk c of the string that starts at byte `byte0` of a digest held as little-endian words.  The string is a
+// big-endian bit string: build the 64-bit big-endian window that contains the chunk (cbl <= 24 bits, so 5 bytes
+// always cover it) and shift.
 __device__ __forceinline__ uint32_t eq_chunk_words(const uint64_t d[8], int byte0, int cbl, int c)
 {
-    uint32_t v = 0;
     const int bit0 = byte0 * 8 + c * cbl;
-    for (int b = 0; b < cbl; ++b) {
-        const int bit = bit0 + b;
-        const uint32_t byte = (uint32_t)(d[bit >> 6] >> (8 * ((bit >> 3) & 7))) & 0xffu;
-        v = (v << 1) | ((byte >> (7 - (bit & 7))) & 1u);
+    const int first = bit0 >> 3;  // first byte of the window
+    uint64_t win = 0;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        const int by = first + i;
+        const uint64_t byte = by < 64 ? (d[by >> 3] >> (8 * (by & 7))) & 0xffull : 0ull;
+        win = (win << 8) | byte;
     }
-    return v;
+    // window = 40 bits, chunk starts (bit0 & 7) bits into it
+    return (uint32_t)((win >> (40 - (bit0 & 7) - cbl)) & ((1ull << cbl) - 1ull));
 }
 
 // chunks of initial string i (used by the validator)
@@ -109,13 +114,14 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
             continue;
         }
         const uint32_t id = b * p.slots + slot;
-        for (int c = 0; c < p.chunks; ++c) rows[(size_t)id * p.chunks + c] = ch[c];
+        for (int c = 0; c < p.chunks; ++c) rows[(size_t)id * p.chunks + c] = ch[c];  // round 0: stride = chunks
         leaf[id] = i;
     }
 }
 
 // ---- one round: one CTA per bucket ----
-// dynamic shared memory: [rows of the bucket: slots x chunks words][order: slots x u16][key: slots x u16]
+// Rows of round r carry only the chunks that are still alive, r..k: their stride is S = chunks - r words.
+// dynamic shared memory: [rows of the bucket: slots x S words][order: slots x u16][key: slots x u16]
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS)
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ bucket_cnt,
                   uint32_t* __restrict__ next_rows, uint32_t* __restrict__ next_cnt, uint2* __restrict__ tree,
@@ -125,9 +131,9 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     __shared__ uint32_t hist[256];
     __shared__ uint32_t start[257];
     __shared__ uint32_t warp_sum[EQ_COLLIDE_THREADS / 32];
-    const uint32_t C = (uint32_t)p.chunks;
+    const uint32_t S = (uint32_t)(p.chunks - r);  // word 0 of a row is chunk r
     uint32_t* const rs = eq_smem;
-    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * C);
+    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * S);
     uint16_t* const key = order + p.slots;
     const uint32_t b = blockIdx.x, t = threadIdx.x;
     const uint32_t cnt = min(bucket_cnt[b], p.slots);
@@ -136,11 +142,11 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     if (cnt == 0) return;
 
     hist[t] = 0;
-    const uint32_t* src = rows + (size_t)base * C;
-    for (uint32_t i = t; i < cnt * C; i += EQ_COLLIDE_THREADS) rs[i] = src[i];  // contiguous: the bucket's rows
+    const uint32_t* src = rows + (size_t)base * S;
+    for (uint32_t i = t; i < cnt * S; i += EQ_COLLIDE_THREADS) rs[i] = src[i];  // contiguous: the bucket's rows
     __syncthreads();
     for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
-        const uint32_t kk = rs[i * C + r] & 0xffu;
+        const uint32_t kk = rs[i * S] & 0xffu;
         key[i] = (uint16_t)kk;
         atomicAdd(&hist[kk], 1u);
     }
@@ -169,13 +175,13 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
         const uint32_t sa = order[i];
         const uint32_t end = start[key[sa] + 1u];
-        const uint32_t* ra = rs + sa * C;
+        const uint32_t* ra = rs + sa * S;
         for (uint32_t j = i + 1; j < end; ++j) {
             const uint32_t sb = order[j];
-            const uint32_t* rb = rs + sb * C;
+            const uint32_t* rb = rs + sb * S;
             uint32_t x[EQ_MAX_CHUNKS];
             uint32_t any = 0;
-            for (uint32_t c = (uint32_t)r + 1; c < C; ++c) {
+            for (uint32_t c = 1; c < S; ++c) {  // word c = chunk r + c
                 x[c] = ra[c] ^ rb[c];
                 any |= x[c];
             }
@@ -189,14 +195,15 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                 if (slot < EQ_MAX_CANDIDATES) tree[slot] = make_uint2(base + sa, base + sb);
             } else {
                 if (any == 0) continue;  // identical remainders: the two subtrees share their index set
-                const uint32_t nb = p.bucket_bits ? (x[r + 1] >> 8) : 0u;
+                const uint32_t nb = p.bucket_bits ? (x[1] >> 8) : 0u;
                 const uint32_t slot = atomicAdd(&next_cnt[nb], 1u);
                 if (slot >= p.slots) {
                     atomicAdd(cand_count + 1, 1u);  // a row that did not fit its bucket is lost: counted, reported
                     continue;
                 }
                 const uint32_t id = nb * p.slots + slot;
-                for (uint32_t c = (uint32_t)r + 1; c < C; ++c) next_rows[(size_t)id * C + c] = x[c];
+                uint32_t* dst = next_rows + (size_t)id * (S - 1);
+                for (uint32_t c = 1; c < S; ++c) dst[c - 1] = x[c];
                 tree[id] = make_uint2(base + sa, base + sb);
             }
         }
@@ -491,7 +498,8 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     ++launches;
     for (int r = 0; r < k; ++r) {
         NX_CUDA(cudaMemsetAsync(s->bucket_cnt[(r + 1) & 1], 0, cnt_bytes, s->stream));
-        eq_collide_kernel<<<p.num_buckets, EQ_COLLIDE_THREADS, s->smem_bytes, s->stream>>>(
+        const size_t smem = (size_t)p.slots * (size_t)(p.chunks - r) * 4 + (size_t)p.slots * 2 * 2;  // fewer live chunks, more CTAs/SM
+        eq_collide_kernel<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
             r >= 1 ? s->tree[r] : nullptr, s->cand_count);
         ++launches;
