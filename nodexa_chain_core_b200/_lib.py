@@ -142,6 +142,7 @@ def _load() -> C.CDLL:
         "nx_kawpow_compile_cubin": (C.c_long, [u64, u32, C.c_char_p, sz]),
         "nx_host_light_cache": (None, [i, vp]),
         "nx_host_light_cache_variant": (i, [i, i, vp]),
+        "nx_host_light_cache_cached": (i, [i, vp]),
         "nx_keccakf1600_avx512": (i, [C.POINTER(u64)]),
     }
     for name, (res, args) in sig.items():

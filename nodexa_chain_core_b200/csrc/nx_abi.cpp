@@ -198,7 +198,10 @@ int create(int epoch, int device, int rank, int world, const uint8_t* light_in, 
         NX_TRY(cudaMemcpyAsync(c->light_host, c->light_dev, light_bytes, cudaMemcpyDeviceToHost, c->stream));
         NX_TRY(cudaStreamSynchronize(c->stream));
     } else {
-        host_build_light_cache(c->light_host, c->light_items, seed);
+        if (!host_load_light_cache(c->light_host, c->light_items, epoch)) {  // NX_CACHE_DIR: reuse an earlier build
+            host_build_light_cache(c->light_host, c->light_items, seed);
+            host_store_light_cache(c->light_host, c->light_items, epoch);
+        }
         NX_TRY(cudaMemcpyAsync(c->light_dev, c->light_host, light_bytes, cudaMemcpyHostToDevice, c->stream));
     }
     c->light_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

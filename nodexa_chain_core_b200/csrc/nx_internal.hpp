@@ -32,6 +32,8 @@ void host_build_light_cache_scalar(uint8_t* cache, int num_items, const uint8_t 
 void host_build_light_cache_avx512(uint8_t* cache, int num_items, const uint8_t seed[32]);  // nx_lightcache_avx512.cpp
 void keccakf1600_avx512(uint64_t a[25]);
 bool cpu_has_avx512f();  // nx_cpu_dispatch.cpp
+bool host_load_light_cache(uint8_t* cache, int num_items, int epoch);        // NX_CACHE_DIR, verified; false = rebuild
+void host_store_light_cache(const uint8_t* cache, int num_items, int epoch);
 
 // ---- program generator (nx_codegen.cpp) ----
 struct ProgramOp

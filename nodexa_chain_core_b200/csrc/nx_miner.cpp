@@ -84,7 +84,10 @@ int build_contexts(const std::vector<int>& devices, int epoch, std::vector<nx_ep
     std::vector<uint8_t> light((size_t)n_light * 64);
     uint8_t seed[32];
     nx_epoch_seed(epoch, seed);
-    host_build_light_cache(light.data(), n_light, seed);
+    if (!host_load_light_cache(light.data(), n_light, epoch)) {
+        host_build_light_cache(light.data(), n_light, seed);
+        host_store_light_cache(light.data(), n_light, epoch);
+    }
 
     const size_t n = devices.size();
     const bool fused = all_peers_reachable(devices);

@@ -88,3 +88,17 @@ int nx_keccakf1600_avx512(uint64_t state[25])
     return 0;
 }
 }
+
+extern "C" {
+// Light cache through the NX_CACHE_DIR file cache (tests): returns 1 when it was served from disk, 0 when built.
+int nx_host_light_cache_cached(int epoch, uint8_t* out)
+{
+    const int n = nx_light_cache_num_items(epoch);
+    if (host_load_light_cache(out, n, epoch)) return 1;
+    uint8_t seed[32];
+    nx_epoch_seed(epoch, seed);
+    host_build_light_cache(out, n, seed);
+    host_store_light_cache(out, n, epoch);
+    return 0;
+}
+}

@@ -157,3 +157,31 @@ def test_wire_header_parse_serialize_and_block_hash(oracle):
         assert h.kawpow_header_hash() == hh
         fin = oracle.kawpow_hash_no_verify(h.height, hh, h.mix_hash[::-1], h.nonce64)
         assert h.block_hash() == fin[::-1]
+
+
+def test_light_cache_file_cache(tmp_path, monkeypatch):
+    """NX_CACHE_DIR: first call builds and writes, second call is served from disk, a corrupted or foreign file
+    is detected and rebuilt - the bytes are always the reference's."""
+    import hashlib
+    e = golden("epochs.json")
+    n = ethash.calculate_light_cache_num_items(0)
+    want = e["light_cache_sha256_epoch0"]
+    buf = C.create_string_buffer(n * 64)
+    monkeypatch.delenv("NX_CACHE_DIR", raising=False)
+    assert lib.nx_host_light_cache_cached(0, buf) == 0              # no directory configured: always built
+    monkeypatch.setenv("NX_CACHE_DIR", str(tmp_path))
+    assert lib.nx_host_light_cache_cached(0, buf) == 0              # first time: built + stored
+    path = tmp_path / "light_cache_epoch0.nxlc"
+    assert path.exists() and path.stat().st_size == n * 64 + 24
+    buf2 = C.create_string_buffer(n * 64)
+    assert lib.nx_host_light_cache_cached(0, buf2) == 1             # second time: from disk
+    assert hashlib.sha256(buf2.raw).hexdigest() == want
+    raw = bytearray(path.read_bytes())
+    raw[24 + 12345] ^= 1                                            # flip one payload bit
+    path.write_bytes(bytes(raw))
+    buf3 = C.create_string_buffer(n * 64)
+    assert lib.nx_host_light_cache_cached(0, buf3) == 0             # checksum mismatch: rebuilt (and rewritten)
+    assert hashlib.sha256(buf3.raw).hexdigest() == want
+    assert lib.nx_host_light_cache_cached(0, buf3) == 1
+    path.write_bytes(path.read_bytes()[:1000])                      # truncated file
+    assert lib.nx_host_light_cache_cached(0, buf3) == 0 and hashlib.sha256(buf3.raw).hexdigest() == want
