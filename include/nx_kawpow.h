@@ -300,7 +300,9 @@ int nx_check_block_headers(const nx_epoch* ctx, const uint8_t* raw_headers /* n 
  * Miner: one process, all GPUs.  Replaces the nonce loops of miner.cpp:656-713 (CloreMiner) and
  * rpc/mining.cpp:117-173 (generateBlocks), and the epoch-context handling of hash.cpp:260-266 /
  * crypto/ethash/lib/ethash/managed.cpp.  Devices claim nonce super-batches in ascending order as they become
- * free; the result is the LOWEST qualifying nonce of the range (host-side min reduction, progpow.cpp:572-577). */
+ * free; the result is the LOWEST qualifying nonce of the range (host-side min reduction, progpow.cpp:572-577).
+ * Threading: one miner serves one mining loop - do not overlap nx_miner_search / _mine_header / _set_epoch calls on the
+ * same miner; nx_miner_prepare_async may run beside them (that is its purpose), and `cancel` may be set from any thread. */
 typedef struct nx_miner nx_miner;
 int nx_miner_create(const int* devices, int n_devices, nx_miner** out); /* devices NULL / n 0 = all visible GPUs */
 void nx_miner_destroy(nx_miner* m);
