@@ -184,40 +184,79 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     __syncthreads();
     for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) order[atomicAdd(&hist[key[i]], 1u)] = (uint16_t)i;
     __syncthreads();
-    // sorted position i pairs with every later position of its key group
-    for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
-        const uint32_t sa = order[i];
-        const uint32_t end = start[key[sa] + 1u];
-        const uint32_t* ra = rs + sa * S;
-        for (uint32_t j = i + 1; j < end; ++j) {
-            const uint32_t sb = order[j];
-            const uint32_t* rb = rs + sb * S;
-            uint32_t x[EQ_MAX_CHUNKS];
-            uint32_t any = 0;
-            for (uint32_t c = 1; c < S; ++c) {  // word c = chunk r + c
-                x[c] = ra[c] ^ rb[c];
-                any |= x[c];
-            }
-            if (last) {
-                if (any != 0) continue;  // the last round must cancel both remaining chunks
-                if (prev_tree) {         // cheap early filter: two rows that share a child share indices
-                    const uint2 pa = prev_tree[base + sa], pb = prev_tree[base + sb];
-                    if (pa.x == pb.x || pa.x == pb.y || pa.y == pb.x || pa.y == pb.y) continue;
-                }
-                const uint32_t slot = atomicAdd(cand_count, 1u);
-                if (slot < EQ_MAX_CANDIDATES) tree[slot] = make_uint2(base + sa, base + sb);
+    // Sorted position i pairs with every later position of its key group.  A thread owns positions t, t+256, ...
+    // (up to EQ_CURSORS of them) and advances them in lock step: per step it first issues the slot-reserving
+    // atomics of all its live cursors, and only then uses the returned slots - so several global atomics per
+    // thread are in flight instead of one (their latency is what this kernel waits on).
+    constexpr int EQ_CURSORS = 4;
+    for (uint32_t i0 = t; i0 < cnt; i0 += EQ_COLLIDE_THREADS * EQ_CURSORS) {
+        uint32_t sa[EQ_CURSORS], j[EQ_CURSORS], end[EQ_CURSORS];
+        bool live = false;
+#pragma unroll
+        for (int c = 0; c < EQ_CURSORS; ++c) {
+            const uint32_t i = i0 + (uint32_t)c * EQ_COLLIDE_THREADS;
+            if (i < cnt) {
+                sa[c] = order[i];
+                end[c] = start[key[sa[c]] + 1u];
+                j[c] = i + 1;
             } else {
-                if (any == 0) continue;  // identical remainders: the two subtrees share their index set
-                const uint32_t nb = p.bucket_bits ? (x[1] >> 8) : 0u;
-                const uint32_t slot = atomicAdd(&next_cnt[nb], 1u);
-                if (slot >= p.slots) {
-                    atomicAdd(cand_count + 1, 1u);  // a row that did not fit its bucket is lost: counted, reported
-                    continue;
+                sa[c] = 0;
+                end[c] = 0;
+                j[c] = 1;
+            }
+            live |= j[c] < end[c];
+        }
+        while (live) {
+            uint32_t slot[EQ_CURSORS], nb[EQ_CURSORS], sb[EQ_CURSORS];
+            bool emit[EQ_CURSORS];
+            // phase A: decide and reserve
+#pragma unroll
+            for (int c = 0; c < EQ_CURSORS; ++c) {
+                emit[c] = false;
+                if (j[c] >= end[c]) continue;
+                sb[c] = order[j[c]];
+                const uint32_t* ra = rs + sa[c] * S;
+                const uint32_t* rb = rs + sb[c] * S;
+                uint32_t any = 0, x1 = 0;
+                for (uint32_t w = 1; w < S; ++w) {  // word w = chunk r + w
+                    const uint32_t x = ra[w] ^ rb[w];
+                    if (w == 1) x1 = x;
+                    any |= x;
                 }
-                const uint32_t id = nb * p.slots + slot;
-                uint32_t* dst = next_rows + (size_t)id * (S - 1);
-                for (uint32_t c = 1; c < S; ++c) dst[c - 1] = x[c];
-                tree[id] = make_uint2(base + sa, base + sb);
+                if (last) {
+                    if (any != 0) continue;  // the last round must cancel both remaining chunks
+                    if (prev_tree) {         // cheap early filter: two rows that share a child share indices
+                        const uint2 pa = prev_tree[base + sa[c]], pb = prev_tree[base + sb[c]];
+                        if (pa.x == pb.x || pa.x == pb.y || pa.y == pb.x || pa.y == pb.y) continue;
+                    }
+                    slot[c] = atomicAdd(cand_count, 1u);
+                } else {
+                    if (any == 0) continue;  // identical remainders: the two subtrees share their index set
+                    nb[c] = p.bucket_bits ? (x1 >> 8) : 0u;
+                    slot[c] = atomicAdd(&next_cnt[nb[c]], 1u);
+                }
+                emit[c] = true;
+            }
+            // phase B: use the reserved slots
+            live = false;
+#pragma unroll
+            for (int c = 0; c < EQ_CURSORS; ++c) {
+                if (emit[c]) {
+                    if (last) {
+                        if (slot[c] < EQ_MAX_CANDIDATES) tree[slot[c]] = make_uint2(base + sa[c], base + sb[c]);
+                    } else if (slot[c] >= p.slots) {
+                        atomicAdd(cand_count + 1, 1u);  // a row that did not fit its bucket is lost: counted, reported
+                    } else {
+                        const uint32_t id = nb[c] * p.slots + slot[c];
+                        const uint32_t* ra = rs + sa[c] * S;
+                        const uint32_t* rb = rs + sb[c] * S;
+                        uint32_t* dst = next_rows + (size_t)id * (S - 1);
+                        for (uint32_t w = 1; w < S; ++w) dst[w - 1] = ra[w] ^ rb[w];
+                        tree[id] = make_uint2(base + sa[c], base + sb[c]);
+                    }
+                }
+                ++j[c];
+                live |= j[c] < end[c];
             }
         }
     }
