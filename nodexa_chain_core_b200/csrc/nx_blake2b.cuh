@@ -40,19 +40,6 @@ NXB_HD uint64_t b2_iv(int i)
 
 NXB_HD void b2_compress(uint64_t h[8], const uint64_t m[16], uint64_t t, bool last)
 {
-    // message schedule sigma, rows 0..9 (rounds 10,11 reuse rows 0,1)
-    const uint8_t S[12][16] = {{0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15},
-                               {14, 10, 4, 8, 9, 15, 13, 6, 1, 12, 0, 2, 11, 7, 5, 3},
-                               {11, 8, 12, 0, 5, 2, 15, 13, 10, 14, 3, 6, 7, 1, 9, 4},
-                               {7, 9, 3, 1, 13, 12, 11, 14, 2, 6, 5, 10, 4, 0, 15, 8},
-                               {9, 0, 5, 7, 2, 4, 10, 15, 14, 1, 11, 12, 6, 8, 3, 13},
-                               {2, 12, 6, 10, 0, 11, 8, 3, 4, 13, 7, 5, 15, 14, 1, 9},
-                               {12, 5, 1, 15, 14, 13, 4, 10, 0, 7, 6, 3, 9, 2, 8, 11},
-                               {13, 11, 7, 14, 12, 1, 3, 9, 5, 0, 15, 4, 8, 6, 2, 10},
-                               {6, 15, 14, 9, 11, 3, 0, 8, 12, 2, 13, 7, 1, 4, 10, 5},
-                               {10, 2, 8, 4, 7, 6, 1, 5, 15, 11, 9, 14, 3, 12, 13, 0},
-                               {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15},
-                               {14, 10, 4, 8, 9, 15, 13, 6, 1, 12, 0, 2, 11, 7, 5, 3}};
     uint64_t v[16];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -70,17 +57,116 @@ NXB_HD void b2_compress(uint64_t h[8], const uint64_t m[16], uint64_t t, bool la
     v[d] = b2_rotr(v[d] ^ v[a], 16);       \
     v[c] = v[c] + v[d];                    \
     v[b] = b2_rotr(v[b] ^ v[c], 63)
-#pragma unroll
-    for (int r = 0; r < 12; ++r) {
-        NXB_G(0, 4, 8, 12, m[S[r][0]], m[S[r][1]]);
-        NXB_G(1, 5, 9, 13, m[S[r][2]], m[S[r][3]]);
-        NXB_G(2, 6, 10, 14, m[S[r][4]], m[S[r][5]]);
-        NXB_G(3, 7, 11, 15, m[S[r][6]], m[S[r][7]]);
-        NXB_G(0, 5, 10, 15, m[S[r][8]], m[S[r][9]]);
-        NXB_G(1, 6, 11, 12, m[S[r][10]], m[S[r][11]]);
-        NXB_G(2, 7, 8, 13, m[S[r][12]], m[S[r][13]]);
-        NXB_G(3, 4, 9, 14, m[S[r][14]], m[S[r][15]]);
-    }
+    // the 12 rounds written out with the message schedule (sigma) as literals, so that m[] and v[] stay in
+    // registers on the GPU (a table lookup would turn them into local-memory arrays)
+    // round 0
+    NXB_G(0, 4, 8, 12, m[0], m[1]);
+    NXB_G(1, 5, 9, 13, m[2], m[3]);
+    NXB_G(2, 6, 10, 14, m[4], m[5]);
+    NXB_G(3, 7, 11, 15, m[6], m[7]);
+    NXB_G(0, 5, 10, 15, m[8], m[9]);
+    NXB_G(1, 6, 11, 12, m[10], m[11]);
+    NXB_G(2, 7, 8, 13, m[12], m[13]);
+    NXB_G(3, 4, 9, 14, m[14], m[15]);
+    // round 1
+    NXB_G(0, 4, 8, 12, m[14], m[10]);
+    NXB_G(1, 5, 9, 13, m[4], m[8]);
+    NXB_G(2, 6, 10, 14, m[9], m[15]);
+    NXB_G(3, 7, 11, 15, m[13], m[6]);
+    NXB_G(0, 5, 10, 15, m[1], m[12]);
+    NXB_G(1, 6, 11, 12, m[0], m[2]);
+    NXB_G(2, 7, 8, 13, m[11], m[7]);
+    NXB_G(3, 4, 9, 14, m[5], m[3]);
+    // round 2
+    NXB_G(0, 4, 8, 12, m[11], m[8]);
+    NXB_G(1, 5, 9, 13, m[12], m[0]);
+    NXB_G(2, 6, 10, 14, m[5], m[2]);
+    NXB_G(3, 7, 11, 15, m[15], m[13]);
+    NXB_G(0, 5, 10, 15, m[10], m[14]);
+    NXB_G(1, 6, 11, 12, m[3], m[6]);
+    NXB_G(2, 7, 8, 13, m[7], m[1]);
+    NXB_G(3, 4, 9, 14, m[9], m[4]);
+    // round 3
+    NXB_G(0, 4, 8, 12, m[7], m[9]);
+    NXB_G(1, 5, 9, 13, m[3], m[1]);
+    NXB_G(2, 6, 10, 14, m[13], m[12]);
+    NXB_G(3, 7, 11, 15, m[11], m[14]);
+    NXB_G(0, 5, 10, 15, m[2], m[6]);
+    NXB_G(1, 6, 11, 12, m[5], m[10]);
+    NXB_G(2, 7, 8, 13, m[4], m[0]);
+    NXB_G(3, 4, 9, 14, m[15], m[8]);
+    // round 4
+    NXB_G(0, 4, 8, 12, m[9], m[0]);
+    NXB_G(1, 5, 9, 13, m[5], m[7]);
+    NXB_G(2, 6, 10, 14, m[2], m[4]);
+    NXB_G(3, 7, 11, 15, m[10], m[15]);
+    NXB_G(0, 5, 10, 15, m[14], m[1]);
+    NXB_G(1, 6, 11, 12, m[11], m[12]);
+    NXB_G(2, 7, 8, 13, m[6], m[8]);
+    NXB_G(3, 4, 9, 14, m[3], m[13]);
+    // round 5
+    NXB_G(0, 4, 8, 12, m[2], m[12]);
+    NXB_G(1, 5, 9, 13, m[6], m[10]);
+    NXB_G(2, 6, 10, 14, m[0], m[11]);
+    NXB_G(3, 7, 11, 15, m[8], m[3]);
+    NXB_G(0, 5, 10, 15, m[4], m[13]);
+    NXB_G(1, 6, 11, 12, m[7], m[5]);
+    NXB_G(2, 7, 8, 13, m[15], m[14]);
+    NXB_G(3, 4, 9, 14, m[1], m[9]);
+    // round 6
+    NXB_G(0, 4, 8, 12, m[12], m[5]);
+    NXB_G(1, 5, 9, 13, m[1], m[15]);
+    NXB_G(2, 6, 10, 14, m[14], m[13]);
+    NXB_G(3, 7, 11, 15, m[4], m[10]);
+    NXB_G(0, 5, 10, 15, m[0], m[7]);
+    NXB_G(1, 6, 11, 12, m[6], m[3]);
+    NXB_G(2, 7, 8, 13, m[9], m[2]);
+    NXB_G(3, 4, 9, 14, m[8], m[11]);
+    // round 7
+    NXB_G(0, 4, 8, 12, m[13], m[11]);
+    NXB_G(1, 5, 9, 13, m[7], m[14]);
+    NXB_G(2, 6, 10, 14, m[12], m[1]);
+    NXB_G(3, 7, 11, 15, m[3], m[9]);
+    NXB_G(0, 5, 10, 15, m[5], m[0]);
+    NXB_G(1, 6, 11, 12, m[15], m[4]);
+    NXB_G(2, 7, 8, 13, m[8], m[6]);
+    NXB_G(3, 4, 9, 14, m[2], m[10]);
+    // round 8
+    NXB_G(0, 4, 8, 12, m[6], m[15]);
+    NXB_G(1, 5, 9, 13, m[14], m[9]);
+    NXB_G(2, 6, 10, 14, m[11], m[3]);
+    NXB_G(3, 7, 11, 15, m[0], m[8]);
+    NXB_G(0, 5, 10, 15, m[12], m[2]);
+    NXB_G(1, 6, 11, 12, m[13], m[7]);
+    NXB_G(2, 7, 8, 13, m[1], m[4]);
+    NXB_G(3, 4, 9, 14, m[10], m[5]);
+    // round 9
+    NXB_G(0, 4, 8, 12, m[10], m[2]);
+    NXB_G(1, 5, 9, 13, m[8], m[4]);
+    NXB_G(2, 6, 10, 14, m[7], m[6]);
+    NXB_G(3, 7, 11, 15, m[1], m[5]);
+    NXB_G(0, 5, 10, 15, m[15], m[11]);
+    NXB_G(1, 6, 11, 12, m[9], m[14]);
+    NXB_G(2, 7, 8, 13, m[3], m[12]);
+    NXB_G(3, 4, 9, 14, m[13], m[0]);
+    // round 10
+    NXB_G(0, 4, 8, 12, m[0], m[1]);
+    NXB_G(1, 5, 9, 13, m[2], m[3]);
+    NXB_G(2, 6, 10, 14, m[4], m[5]);
+    NXB_G(3, 7, 11, 15, m[6], m[7]);
+    NXB_G(0, 5, 10, 15, m[8], m[9]);
+    NXB_G(1, 6, 11, 12, m[10], m[11]);
+    NXB_G(2, 7, 8, 13, m[12], m[13]);
+    NXB_G(3, 4, 9, 14, m[14], m[15]);
+    // round 11
+    NXB_G(0, 4, 8, 12, m[14], m[10]);
+    NXB_G(1, 5, 9, 13, m[4], m[8]);
+    NXB_G(2, 6, 10, 14, m[9], m[15]);
+    NXB_G(3, 7, 11, 15, m[13], m[6]);
+    NXB_G(0, 5, 10, 15, m[1], m[12]);
+    NXB_G(1, 6, 11, 12, m[0], m[2]);
+    NXB_G(2, 7, 8, 13, m[11], m[7]);
+    NXB_G(3, 4, 9, 14, m[5], m[3]);
 #undef NXB_G
 #pragma unroll
     for (int i = 0; i < 8; ++i) h[i] ^= v[i] ^ v[i + 8];
