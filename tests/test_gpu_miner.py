@@ -94,3 +94,53 @@ def test_failed_device_drops_out_and_its_windows_are_reissued(nx, ctx_of, monkey
             assert m.last_failed_devices == 1
         monkeypatch.delenv("NX_MINER_INJECT_FAIL")
         assert m.search(900, hd, boundary, 1 << 50, n) == want and m.last_failed_devices == 0
+
+
+def test_cancel_flag_stops_a_long_search(nx):
+    """miner.cpp:693-712: the outer loop must be able to abandon the scan (new tip, stale template)."""
+    import threading
+    import time
+    with nx.Miner([0]) as m:
+        m.set_epoch(0)
+        m.set_batch(1 << 20)
+        m.search(5, bytes(32), bytes(32), 0, 1 << 20)  # compile the period program first
+        out = {}
+
+        def run():
+            t0 = time.perf_counter()
+            out["r"] = m.search(5, bytes(32), bytes(32), 0, 1 << 40)  # ~90 minutes of work if left alone
+            out["s"] = time.perf_counter() - t0
+
+        th = threading.Thread(target=run)
+        th.start()
+        time.sleep(0.3)
+        m.cancel()
+        th.join(timeout=30)
+        assert not th.is_alive() and out["s"] < 5.0
+        assert not out["r"].solution_found
+        hashes, _ = m.last_stats()
+        assert 0 < hashes < 1 << 34
+
+
+def test_program_cache_dir_persists_compiled_periods(tmp_path):
+    """NX_PROGRAM_CACHE_DIR: the cubin of a period is written once and reused by the next process."""
+    import os
+    import subprocess
+    import sys
+
+    from conftest import ROOT
+    code = ("import nodexa_chain_core_b200 as nx; from nodexa_chain_core_b200 import progpow;"
+            "c = nx.create_epoch_context(0, 0); print(progpow.hash_batch(c, 300, bytes(32), 0, 4).hex()); c.close()")
+    env = dict(os.environ, NX_PROGRAM_CACHE_DIR=str(tmp_path), NX_VERBOSE="1")
+    first = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert first.returncode == 0, first.stderr[-2000:]
+    files = sorted(os.listdir(tmp_path))
+    assert len(files) == 1 and files[0].startswith("kawpow_sm_100a_100_4194296_") and files[0].endswith(".cubin")
+    second = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert second.returncode == 0 and second.stdout == first.stdout
+    assert sorted(os.listdir(tmp_path)) == files
+
+    def compile_ms(stderr):
+        import re
+        return float(re.search(r": ([0-9.]+) ms, regs", stderr).group(1))
+    assert compile_ms(second.stderr) < compile_ms(first.stderr)  # loading a cubin beats NVRTC
