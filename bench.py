@@ -168,7 +168,7 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=120)  # ~10.5 s of steady state at N=1
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=1 << 24, help="nonces per step per GPU")
     ap.add_argument("--epoch", type=int, default=EPOCH)
@@ -279,6 +279,20 @@ def main():
     barrier()
     e2e_s = time.perf_counter() - e0
 
+    # ---- found-nonce plumbing (not timed): a boundary that ~4 of 2^26 nonces meet; the hit must verify ----
+    plumbing = None
+    if rank == 0:
+        easy = bytes.fromhex("000000ff" + "ff" * 28)
+        hdp = header_for(7777, ethash.keccak256)
+        sr_hit = progpow.search(ctx, height, hdp, easy, 7777 << 32, 1 << 26)
+        plumbing = {"boundary": easy.hex()[:10] + "...", "range": "2^26 nonces", "found": sr_hit.solution_found}
+        if sr_hit.solution_found:
+            plumbing["nonce"] = sr_hit.nonce
+            plumbing["verified"] = bool(progpow.verify(ctx, height, hdp, sr_hit.mix_hash, sr_hit.nonce, easy)
+                                        and sr_hit.final_hash <= easy
+                                        and progpow.hash_no_verify(height, hdp, sr_hit.mix_hash, sr_hit.nonce) == sr_hit.final_hash)
+            assert plumbing["verified"], "a found nonce failed verification"
+
     # ---- max over ranks ----
     t = torch.tensor([kernel_ms, e2e_s * 1e3, wall_s * 1e3, dag_ms, light_ms, allgather_ms], dtype=torch.float64,
                      device=f"cuda:{local}")
@@ -325,6 +339,7 @@ def main():
                          "algorithmic_bytes_per_hash": DAG_BYTES_PER_HASH, "kernel": "nx_kawpow_search_kernel",
                          "roofline_mhs": peak * 1e9 / DAG_BYTES_PER_HASH / 1e6},
             "clocks": clocks,
+            "found_nonce_plumbing": plumbing,
             "epoch_build": {"light_cache_ms": light_ms, "dag_kernel_ms": dag_ms, "allgather_ms": allgather_ms,
                             "total_s": build_s, "dag_gbs_written": ctx.dag_bytes / world / (dag_ms * 1e-3) / 1e9},
         }

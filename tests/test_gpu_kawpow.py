@@ -205,3 +205,21 @@ def test_concurrent_host_threads_share_one_context(ctx_of):
     for x in th:
         x.join()
     assert not errors, errors
+
+
+def test_epoch448_1024_nonces_and_4096_dag_items_vs_reference_live(ctx_of, ref):
+    """SURVEY.md §8(d) config 2's parity spot check at the bench's own epoch, against the reference's compiled
+    code running on this box's host cores: 1024 consecutive nonces (light path) and 4096 random DAG items."""
+    ctx = ctx_of(448)
+    height = 448 * 7500 + 11
+    hd = hashlib.sha256(b"epoch448-live").digest()
+    start = 0x448 << 40
+    want = ref.kawpow_hash_range(448, height, hd, start, 1024)
+    assert progpow.hash_batch(ctx, height, hd, start, 1024) == want
+    rnd = random.Random(448)
+    m = ctx.dag_num_items
+    idx = sorted(rnd.randrange(m) for _ in range(4096))
+    for i in idx[::64]:  # 64 single-item reads spread over the DAG ...
+        assert ctx.read_items(i, 1) == ref.dataset_item_2048(448, i)
+    first = rnd.randrange(m - 4096)  # ... and one run of 4096 consecutive items
+    assert ctx.read_items(first, 4096) == ref.dataset_items_2048(448, first, 4096)
