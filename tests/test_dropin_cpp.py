@@ -55,3 +55,23 @@ def test_reference_kawpow_test_cases_through_cpp_dropin(tmp_path, gpu):
     exe = _build(tmp_path)
     out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "ALL OK" in out.stdout, out.stdout[-3000:] + out.stderr[-2000:]
+
+
+def _build_c_example(tmp_path):
+    libdir = os.path.join(ROOT, "nodexa_chain_core_b200")
+    exe = tmp_path / "mine_and_verify"
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "mine_and_verify.c"), "-o", str(exe), "-L", libdir, "-lnxkawpow",
+                           f"-Wl,-rpath,{libdir}"])
+    return exe
+
+
+def test_c_example_compiles(tmp_path):
+    _build_c_example(tmp_path)
+
+
+@pytest.mark.gpu
+def test_c_example_mines_and_verifies(tmp_path, gpu):
+    """examples/mine_and_verify.c: the node-side flow in plain C99 over the C ABI."""
+    out = subprocess.run([str(_build_c_example(tmp_path))], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and out.stdout.strip().endswith("OK"), out.stdout[-1000:] + out.stderr[-1000:]
