@@ -81,7 +81,9 @@ void l2_pin_light_cache(nx_epoch* c, bool on)
         cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
         if (max_persist <= 0 || max_window <= 0) return;
         const size_t light_bytes = (size_t)c->light_items * 64;
+        if (!c->l2_pinned) cudaDeviceGetLimit(&c->l2_prev_limit, cudaLimitPersistingL2CacheSize);
         cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist);
+        c->l2_pinned = true;
         const size_t window = light_bytes < (size_t)max_window ? light_bytes : (size_t)max_window;
         attr.accessPolicyWindow.base_ptr = c->light_dev;
         attr.accessPolicyWindow.num_bytes = window;
@@ -89,14 +91,26 @@ void l2_pin_light_cache(nx_epoch* c, bool on)
         attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
         attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
     } else {
+        if (!c->l2_pinned) return;
         attr.accessPolicyWindow.num_bytes = 0;
         attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
         attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
     }
     cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr);
-    if (!on) cudaCtxResetPersistingL2Cache();
+    if (!on) {  // hand the L2 back exactly as the host process had it
+        cudaCtxResetPersistingL2Cache();
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, c->l2_prev_limit);
+        c->l2_pinned = false;
+    }
     cudaGetLastError();
 }
+
+struct L2Pin  // pinned for the scope, released on every exit path
+{
+    nx_epoch* c;
+    explicit L2Pin(nx_epoch* ctx) : c(ctx) { l2_pin_light_cache(c, true); }
+    ~L2Pin() { l2_pin_light_cache(c, false); }
+};
 
 int program_for(const nx_epoch* c, int block_number, std::shared_ptr<KawpowProgram>* p)
 {
@@ -108,6 +122,7 @@ void destroy(nx_epoch* c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->l2_pinned) l2_pin_light_cache(c, false);  // a create() that failed between pin and unpin
     for (void* p : c->ipc_opened) cudaIpcCloseMemHandle(p);
     if (c->dag_dev) cudaFree(c->dag_dev);
     if (c->light_dev) cudaFree(c->light_dev);
@@ -305,13 +320,14 @@ static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries;
         if (r != c->rank) outs[n++] = (char*)peer_bases[r] + (size_t)first * 256;
     std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
-    l2_pin_light_cache(c, true);
-    NX_CUDA(cudaEventRecord(c->ev0, c->stream));
-    const int rc = dag_generate_multi(c->light_dev, c->light_items, first, count, outs, n, c->stream);
-    if (rc != NX_OK) return rc;
-    NX_CUDA(cudaEventRecord(c->ev1, c->stream));
-    NX_CUDA(cudaStreamSynchronize(c->stream));
-    l2_pin_light_cache(c, false);
+    {
+        L2Pin pin(c);
+        NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+        const int rc = dag_generate_multi(c->light_dev, c->light_items, first, count, outs, n, c->stream);
+        if (rc != NX_OK) return rc;
+        NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+        NX_CUDA(cudaStreamSynchronize(c->stream));
+    }
     float ms = 0;
     NX_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     c->dag_ms = ms;
@@ -319,7 +335,7 @@ static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries;
     return NX_OK;
 }
 
-int nx_epoch_generate_fused_ipc(nx_epoch* c, const uint8_t* handles /* world x 64 bytes, indexed by rank */)
+static int nx_epoch_generate_fused_ipc_body(nx_epoch* c, const uint8_t* handles /* world x 64 bytes, indexed by rank */)
 {
     if (!c || !handles) {
         set_error("null argument");
@@ -406,13 +422,14 @@ int nx_dag_generate_range(const nx_epoch* cc, uint32_t first, uint32_t count, vo
     }
     std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
-    l2_pin_light_cache(c, true);
-    NX_CUDA(cudaEventRecord(c->ev0, c->stream));
-    int rc = dag_generate(c->light_dev, c->light_items, first, count, out_device, c->stream);
-    if (rc != NX_OK) return rc;
-    NX_CUDA(cudaEventRecord(c->ev1, c->stream));
-    NX_CUDA(cudaStreamSynchronize(c->stream));
-    l2_pin_light_cache(c, false);
+    {
+        L2Pin pin(c);
+        NX_CUDA(cudaEventRecord(c->ev0, c->stream));
+        int rc = dag_generate(c->light_dev, c->light_items, first, count, out_device, c->stream);
+        if (rc != NX_OK) return rc;
+        NX_CUDA(cudaEventRecord(c->ev1, c->stream));
+        NX_CUDA(cudaStreamSynchronize(c->stream));
+    }
     NX_CUDA(cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1));
     c->last_launches = 1;
     return NX_OK;
@@ -743,7 +760,7 @@ int nx_kawpow_verify(const nx_epoch* c, int block_number, const uint8_t header_h
     return std::memcmp(r.mix_hash, mix_hash, 32) == 0 ? 1 : 0;
 }
 
-int nx_kawpow_hash_many(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host)
+static int nx_kawpow_hash_many_body(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host)
 {
     nx_epoch* c = const_cast<nx_epoch*>(cc);
     int rc = check_ctx(c, 0);
@@ -809,7 +826,7 @@ int nx_kawpow_hash_many(const nx_epoch* cc, const nx_hash_record* records, size_
     return NX_OK;
 }
 
-int nx_check_block_headers(const nx_epoch* c, const uint8_t* raw, size_t n, const uint8_t pow_limit_be[32], int mix_only,
+static int nx_check_block_headers_body(const nx_epoch* c, const uint8_t* raw, size_t n, const uint8_t pow_limit_be[32], int mix_only,
                            uint8_t* status)
 {
     if ((!raw || !status) && n) {
@@ -870,7 +887,7 @@ int nx_check_block_headers(const nx_epoch* c, const uint8_t* raw, size_t n, cons
     return NX_OK;
 }
 
-int nx_kawpow_verify_batch(const nx_epoch* c, const nx_verify_record* records, size_t n, uint8_t* ok)
+static int nx_kawpow_verify_batch_body(const nx_epoch* c, const nx_verify_record* records, size_t n, uint8_t* ok)
 {
     if ((!records || !ok) && n) {
         set_error("null argument");
@@ -900,6 +917,27 @@ int nx_kawpow_verify_batch(const nx_epoch* c, const nx_verify_record* records, s
     for (size_t k = 0; k < todo.size(); ++k)
         ok[index[k]] = std::memcmp(out.data() + 64 * k + 32, records[index[k]].mix_hash, 32) == 0 ? 1 : 0;
     return NX_OK;
+}
+
+int nx_epoch_generate_fused_ipc(nx_epoch* c, const uint8_t* handles /* world x 64 bytes, indexed by rank */)
+{
+    return guarded([&] { return nx_epoch_generate_fused_ipc_body(c, handles); });
+}
+
+int nx_kawpow_hash_many(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host)
+{
+    return guarded([&] { return nx_kawpow_hash_many_body(cc, records, n, out_host); });
+}
+
+int nx_check_block_headers(const nx_epoch* c, const uint8_t* raw, size_t n, const uint8_t pow_limit_be[32], int mix_only,
+                           uint8_t* status)
+{
+    return guarded([&] { return nx_check_block_headers_body(c, raw, n, pow_limit_be, mix_only, status); });
+}
+
+int nx_kawpow_verify_batch(const nx_epoch* c, const nx_verify_record* records, size_t n, uint8_t* ok)
+{
+    return guarded([&] { return nx_kawpow_verify_batch_body(c, records, n, ok); });
 }
 
 }  // extern "C"

@@ -6,6 +6,8 @@
 #include <cstdio>
 #include <memory>
 #include <mutex>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -25,6 +27,24 @@ void clear_error();
             return NX_ERR_CUDA;                                                                    \
         }                                                                                          \
     } while (0)
+
+// "None throws" (include/nx_kawpow.h): entry points that allocate on the host run their body through this.
+template <class F>
+int guarded(F&& body) noexcept
+{
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        set_error("out of host memory");
+        return NX_ERR_OOM;
+    } catch (const std::exception& e) {
+        set_error("unexpected host error: %s", e.what());
+        return NX_ERR_STATE;
+    } catch (...) {
+        set_error("unexpected host error");
+        return NX_ERR_STATE;
+    }
+}
 
 // ---- host algorithms (nx_host.cpp) ----
 void host_build_light_cache(uint8_t* cache, int num_items, const uint8_t seed[32]);  // dispatches on the CPU
@@ -128,6 +148,8 @@ struct nx_epoch
     float last_kernel_ms = 0.f;
     int last_launches = 0;
     double light_ms = 0, dag_ms = 0;
+    bool l2_pinned = false;       // light cache currently marked persisting in L2 (DAG generation only)
+    size_t l2_prev_limit = 0;     // device's persisting-L2 carve-out before we raised it; restored on unpin
     std::recursive_mutex mu;  // serialises use of the stream + scratch; recursive so that a whole search
                               // (enqueue, sync, re-hash of the hit) is one critical section
 };

@@ -147,6 +147,8 @@ namespace
 {
 std::mutex g_cache_mu;
 std::map<std::tuple<int, uint64_t, uint32_t>, std::shared_ptr<KawpowProgram>> g_cache;
+std::mutex g_compile_mu;
+std::map<std::pair<uint64_t, uint32_t>, std::shared_ptr<const std::vector<char>>> g_cubins;  // device independent
 
 int compile_cubin(uint64_t prog_seed, uint32_t dag_items, std::vector<char>& cubin, std::string& log)
 {
@@ -212,14 +214,19 @@ bool kawpow_program_is_cached(int device, uint64_t prog_seed, uint32_t dag_items
     return g_cache.count(std::make_tuple(device, prog_seed, dag_items)) != 0;
 }
 
-int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<KawpowProgram>* out)
+// Three steps with separate locks, so that a cached lookup (every search call makes one) never waits behind another
+// thread's compilation of the next period: (1) map lookup under g_cache_mu; (2) cubin for (prog_seed, dag_items) under
+// g_compile_mu - one NVRTC run serves every device of the process; (3) per-device module load, then publish.
+static int get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<KawpowProgram>* out)
 {
-    std::lock_guard<std::mutex> lk(g_cache_mu);
     const auto key = std::make_tuple(device, prog_seed, dag_items);
-    auto it = g_cache.find(key);
-    if (it != g_cache.end()) {
-        *out = it->second;
-        return NX_OK;
+    {
+        std::lock_guard<std::mutex> lk(g_cache_mu);
+        auto it = g_cache.find(key);
+        if (it != g_cache.end()) {
+            *out = it->second;
+            return NX_OK;
+        }
     }
     Driver& d = driver();
     if (!d.ok) {
@@ -230,27 +237,40 @@ int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
     NX_CUDA(cudaFree(nullptr));  // make sure the primary context exists and is current
 
     const auto t0 = std::chrono::steady_clock::now();
-    std::vector<char> cubin;
-    const char* arch_env = std::getenv("NX_KAWPOW_ARCH");
-    const std::string path = cache_path(prog_seed, dag_items, arch_env && *arch_env ? arch_env : "sm_100a");
-    if (!path.empty()) {
-        std::ifstream f(path, std::ios::binary);
-        if (f) cubin.assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
-    }
-    if (cubin.empty()) {
-        std::string log;
-        const int rc = compile_cubin(prog_seed, dag_items, cubin, log);
-        if (rc != NX_OK) return rc;
-        if (!path.empty()) {
-            std::ofstream f(path, std::ios::binary);
-            f.write(cubin.data(), (std::streamsize)cubin.size());
+    std::shared_ptr<const std::vector<char>> cubin;
+    {
+        std::lock_guard<std::mutex> lk(g_compile_mu);
+        const auto ckey = std::make_pair(prog_seed, dag_items);
+        auto it = g_cubins.find(ckey);
+        if (it != g_cubins.end()) {
+            cubin = it->second;
+        } else {
+            auto fresh = std::make_shared<std::vector<char>>();
+            const char* arch_env = std::getenv("NX_KAWPOW_ARCH");
+            const std::string path = cache_path(prog_seed, dag_items, arch_env && *arch_env ? arch_env : "sm_100a");
+            if (!path.empty()) {
+                std::ifstream f(path, std::ios::binary);
+                if (f) fresh->assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
+            }
+            if (fresh->empty()) {
+                std::string log;
+                const int rc = compile_cubin(prog_seed, dag_items, *fresh, log);
+                if (rc != NX_OK) return rc;
+                if (!path.empty()) {
+                    std::ofstream f(path, std::ios::binary);
+                    f.write(fresh->data(), (std::streamsize)fresh->size());
+                }
+            }
+            while (g_cubins.size() >= 8) g_cubins.erase(g_cubins.begin());  // lowest period first: heights ascend
+            g_cubins[ckey] = fresh;
+            cubin = fresh;
         }
     }
     std::shared_ptr<KawpowProgram> p(new KawpowProgram);
     p->device = device;
     p->prog_seed = prog_seed;
     p->dag_items = dag_items;
-    CUresult_ r = d.ModuleLoadData(&p->module, cubin.data());
+    CUresult_ r = d.ModuleLoadData(&p->module, cubin->data());
     if (r != 0) {
         set_error("cuModuleLoadData failed: %s", cu_err(r));
         return NX_ERR_CUDA;
@@ -279,12 +299,28 @@ int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
         fprintf(stderr, "[nx] kawpow program seed=%llu items=%u tune=%s: %.1f ms, regs hash=%d search=%d smem=%zu\n",
                 (unsigned long long)prog_seed, dag_items, tune().tag().c_str(), p->compile_ms, p->regs_hash,
                 p->regs_search, p->smem_bytes);
-    // keep the cache bounded: a node only needs the current and the next period.  Evicted programs
-    // are unloaded when their last user lets go of the shared_ptr.
-    if (g_cache.size() >= 32) g_cache.clear();
-    *out = p;
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    auto it = g_cache.find(key);
+    if (it != g_cache.end()) {  // another thread loaded the same program meanwhile: keep one
+        *out = it->second;
+        return NX_OK;
+    }
+    // keep the cache bounded: a node needs the current and the next period per device.  The lowest period goes first;
+    // an evicted program is unloaded when its last user lets go of the shared_ptr.
+    while (g_cache.size() >= 64) {
+        auto victim = g_cache.begin();
+        for (auto jt = g_cache.begin(); jt != g_cache.end(); ++jt)
+            if (std::get<1>(jt->first) < std::get<1>(victim->first)) victim = jt;
+        g_cache.erase(victim);
+    }
     g_cache[key] = p;
+    *out = p;
     return NX_OK;
+}
+
+int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<KawpowProgram>* out)
+{
+    return guarded([&] { return get_program(device, prog_seed, dag_items, out); });
 }
 
 static int launch(const KawpowProgram* p, CUfunction_ fn, const void* dag, const KawpowJob& job, void* third,

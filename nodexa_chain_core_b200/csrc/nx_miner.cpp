@@ -125,7 +125,7 @@ int build_contexts(const std::vector<int>& devices, int epoch, std::vector<nx_ep
 
 extern "C" {
 
-int nx_miner_create(const int* devices, int n_devices, nx_miner** out)
+static int nx_miner_create_body(const int* devices, int n_devices, nx_miner** out)
 {
     if (!out) {
         set_error("null out pointer");
@@ -137,21 +137,19 @@ int nx_miner_create(const int* devices, int n_devices, nx_miner** out)
         set_error("no CUDA device: this library has no CPU fallback");
         return NX_ERR_CUDA;
     }
-    nx_miner* m = new (std::nothrow) nx_miner;
-    if (!m) return NX_ERR_OOM;
+    std::unique_ptr<nx_miner> m(new nx_miner);
     if (!devices || n_devices <= 0) {
         for (int d = 0; d < have; ++d) m->devices.push_back(d);  // all visible devices
     } else {
         for (int i = 0; i < n_devices; ++i) {
             if (devices[i] < 0 || devices[i] >= have) {
                 set_error("device %d out of range (have %d)", devices[i], have);
-                delete m;
                 return NX_ERR_INVALID;
             }
             m->devices.push_back(devices[i]);
         }
     }
-    *out = m;
+    *out = m.release();
     return NX_OK;
 }
 
@@ -177,7 +175,7 @@ int nx_miner_set_batch(nx_miner* m, uint64_t nonces_per_batch)
 }
 
 // Make `epoch` current on every device: adopts the contexts prepared in the background when they match.
-int nx_miner_set_epoch(nx_miner* m, int epoch)
+static int nx_miner_set_epoch_body(nx_miner* m, int epoch)
 {
     if (!m || epoch < 0) {
         set_error("bad argument");
@@ -205,7 +203,7 @@ int nx_miner_set_epoch(nx_miner* m, int epoch)
 
 // Background preparation for the blocks after `block_number`: the next period's program on every device,
 // and - when the next epoch starts within `lookahead_blocks` - that epoch's contexts.  Returns at once.
-int nx_miner_prepare_async(nx_miner* m, int block_number, int lookahead_blocks)
+static int nx_miner_prepare_async_body(nx_miner* m, int block_number, int lookahead_blocks)
 {
     if (!m || block_number < 0) {
         set_error("bad argument");
@@ -254,7 +252,7 @@ int nx_miner_wait_prepared(nx_miner* m)
 {
     if (!m) return NX_ERR_INVALID;
     if (!m->background.valid()) return NX_OK;
-    return m->background.get();
+    return guarded([&] { return m->background.get(); });  // get() rethrows whatever the background task threw
 }
 
 int nx_miner_epoch(const nx_miner* m) { return m ? m->epoch : -1; }
@@ -268,7 +266,7 @@ const nx_epoch* nx_miner_context(const nx_miner* m, int index)
 
 // progpow::search over all devices.  `cancel` (may be NULL) is polled between batches: a non-zero value makes
 // the call return early with found = 0 unless a hit was already confirmed as the lowest.
-int nx_miner_search(nx_miner* m, int block_number, const uint8_t header_hash[32], const uint8_t boundary[32],
+static int nx_miner_search_body(nx_miner* m, int block_number, const uint8_t header_hash[32], const uint8_t boundary[32],
                     uint64_t start_nonce, uint64_t iterations, const volatile int* cancel, nx_search_result* out)
 {
     if (!m || !header_hash || !boundary || !out) {
@@ -420,6 +418,27 @@ int nx_miner_mine_header(nx_miner* m, int32_t version, const uint8_t prev_block[
     }
     nx_kawpow_header_hash(version, prev_block, merkle_root, time, bits, height, header_hash);
     return nx_miner_search(m, (int)height, header_hash, boundary, start_nonce, max_tries, cancel, out);
+}
+
+int nx_miner_create(const int* devices, int n_devices, nx_miner** out)
+{
+    return guarded([&] { return nx_miner_create_body(devices, n_devices, out); });
+}
+
+int nx_miner_set_epoch(nx_miner* m, int epoch)
+{
+    return guarded([&] { return nx_miner_set_epoch_body(m, epoch); });
+}
+
+int nx_miner_prepare_async(nx_miner* m, int block_number, int lookahead_blocks)
+{
+    return guarded([&] { return nx_miner_prepare_async_body(m, block_number, lookahead_blocks); });
+}
+
+int nx_miner_search(nx_miner* m, int block_number, const uint8_t header_hash[32], const uint8_t boundary[32],
+                    uint64_t start_nonce, uint64_t iterations, const volatile int* cancel, nx_search_result* out)
+{
+    return guarded([&] { return nx_miner_search_body(m, block_number, header_hash, boundary, start_nonce, iterations, cancel, out); });
 }
 
 }  // extern "C"

@@ -223,3 +223,25 @@ def test_epoch448_1024_nonces_and_4096_dag_items_vs_reference_live(ctx_of, ref):
         assert ctx.read_items(i, 1) == ref.dataset_item_2048(448, i)
     first = rnd.randrange(m - 4096)  # ... and one run of 4096 consecutive items
     assert ctx.read_items(first, 4096) == ref.dataset_items_2048(448, first, 4096)
+
+
+def test_cached_period_is_not_blocked_by_a_compile_in_another_thread(ctx_of):
+    """The miner compiles period p+1 in the background while period p is being searched: a lookup of the cached
+    program must not queue behind that NVRTC run (nx_kawpow_rt.cpp keeps the map lock and the compile lock apart)."""
+    import threading
+    import time
+
+    ctx = ctx_of(0)
+    progpow.prepare(ctx, 3000)  # period 1000, now cached
+    t0 = time.perf_counter()
+    progpow.prepare(ctx, 3003)  # a fresh period: one full compile, for scale
+    compile_s = time.perf_counter() - t0
+    th = threading.Thread(target=progpow.prepare, args=(ctx, 3006))  # ctypes releases the GIL during the call
+    th.start()
+    time.sleep(min(0.05, compile_s / 4))  # let it get into NVRTC
+    t0 = time.perf_counter()
+    got = progpow.hash_batch(ctx, 3000, bytes(32), 0, 64)
+    cached_s = time.perf_counter() - t0
+    th.join()
+    assert len(got) == 64 * 64
+    assert cached_s < 0.5 * compile_s, (cached_s, compile_s)
