@@ -192,9 +192,10 @@ int create(int epoch, int device, int rank, int world, const uint8_t* light_in, 
     NX_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     NX_TRY(cudaEventCreate(&c->ev0));
     NX_TRY(cudaEventCreate(&c->ev1));
-    NX_TRY(cudaMallocHost((void**)&c->light_host, light_bytes));
-    NX_TRY(cudaMalloc(&c->light_dev, light_bytes));
+    // the DAG first: it is the allocation that fails when an epoch does not fit the device, and failing here costs nothing
     NX_TRY(cudaMalloc(&c->dag_dev, c->dag_padded_bytes + 256));  // +1 item: classic Ethash reaches 128-byte item n-1
+    NX_TRY(cudaMalloc(&c->light_dev, light_bytes));
+    NX_TRY(cudaMallocHost((void**)&c->light_host, light_bytes));
     NX_TRY(cudaMalloc((void**)&c->found_min_dev, 2 * sizeof(uint64_t)));
     NX_TRY(cudaMallocHost((void**)&c->found_min_host, 2 * sizeof(uint64_t)));
     NX_TRY(cudaMalloc((void**)&c->checksum_partials_dev, CHECKSUM_PARTIALS * sizeof(uint64_t)));

@@ -124,3 +124,15 @@ def test_two_gpu_sharded_build_and_search(nx):
                          cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert '"multigpu_check": "ok"' in out.stdout
+
+
+def test_epoch_that_does_not_fit_the_device_fails_cleanly(nx, gpu, ctx_of):
+    """ethash.cpp:147-148: the reference returns nullptr when the context cannot be allocated.  Epoch 29999 wants a
+    235 GiB DAG (more than a B200 has): NX_ERR_OOM with a message, nothing leaked, and the device still works."""
+    from nodexa_chain_core_b200._lib import NxError
+
+    with pytest.raises(NxError) as e:
+        nx.create_epoch_context_full(29999, gpu)
+    assert e.value.code == -4 and "cudaMalloc" in str(e.value)
+    ctx = ctx_of(0)
+    assert ctx.l1_cache[:20] == golden("kawpow_kats.json")["l1_epoch0_first20"]
