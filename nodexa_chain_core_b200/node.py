@@ -66,3 +66,55 @@ def check_block_headers(context: EpochContext, headers, pow_limit: bytes = KAWPO
     st = outb(max(1, len(raws)))
     check(lib.nx_check_block_headers(context._h, inb(blob) if blob else outb(1), len(raws), inb(pow_limit), int(mix_only), st))
     return [st[i] for i in range(len(raws))]
+
+
+# ---- the external-miner RPC surface (src/rpc/mining.cpp:722-737 getblocktemplate fields, :763-840 getkawpowhash,
+# :842-880 pprpcsb's proof-of-work gate).  Hex strings are in the order the node prints them: `GetHex()` of a uint256
+# that was itself made by `uint256S(to_hex(hash256))`, i.e. plain hex of the ProgPoW byte order used by the C ABI. ----
+
+def pprpc_fields(header: BlockHeader) -> dict:
+    """`pprpcheader` / `pprpcepoch` of getblocktemplate (mining.cpp:728-736) for a block template."""
+    return {"pprpcheader": header.kawpow_header_hash().hex(), "pprpcepoch": header.height // 7500}
+
+
+def _parse_hex_nonce(text: str) -> int:
+    """ParseUInt64(str, &n, 16): optional 0x prefix, must fit 64 bits (mining.cpp:784-786 'Invalid nonce hex string')."""
+    t = text.strip()
+    try:
+        n = int(t, 16)
+    except ValueError:
+        raise ValueError("Invalid nonce hex string") from None
+    if t.startswith("-") or n >> 64:
+        raise ValueError("Invalid nonce hex string")
+    return n
+
+
+def _uint256s(text: str) -> bytes:
+    """uint256S(hex) printed back with GetHex(): leading blanks and "0x" skipped, short strings zero-extended on the left."""
+    t = text.strip()
+    if t[:2] in ("0x", "0X"):
+        t = t[2:]
+    return bytes.fromhex(t.zfill(64)[-64:])
+
+
+def getkawpowhash(context: EpochContext, header_hash: str, mix_hash: str, nonce: str, height: int, target: str | None = None) -> dict:
+    """The getkawpowhash RPC (mining.cpp:763-840): one KawPow hash on the GPU, compared with the miner's claimed mix
+    and, when a target is given, with that target.  Same keys and "true"/"false" strings as the node's reply."""
+    from . import progpow
+    r = progpow.hash(context, height, bytes.fromhex(header_hash), _parse_hex_nonce(nonce))
+    ret = {"result": "true" if r.mix_hash == _uint256s(mix_hash) else "false",
+           "digest": r.final_hash.hex(), "mix_hash": r.mix_hash.hex(), "info": ""}
+    if target is not None:
+        ret["meets_target"] = "true" if r.final_hash <= _uint256s(target) else "false"
+    return ret
+
+
+def pprpcsb_check(context: EpochContext, template: BlockHeader, mix_hash: str, nonce: str, pow_limit: bytes = KAWPOW_LIMIT):
+    """The proof-of-work gate of pprpcsb (mining.cpp:862-880): the miner's nonce and mix go into the stored template,
+    the full hash is recomputed (GetHashFull) and checked against nBits.  Returns (accepted, filled-in header); the
+    mix itself is compared later, by CheckBlockHeader - see check_block_headers()."""
+    from . import progpow
+    filled = BlockHeader(template.version, template.prev_block, template.merkle_root, template.time, template.bits,
+                         template.height, _parse_hex_nonce(nonce), _uint256s(mix_hash)[::-1])
+    r = progpow.hash(context, filled.height, filled.kawpow_header_hash(), filled.nonce64)
+    return check_proof_of_work(r.final_hash, filled.bits, pow_limit), filled

@@ -130,3 +130,39 @@ def test_check_block_headers_like_the_node(nx, ctx_of, oracle):
     got = node.check_block_headers(ctx, [bad_mix, good[5]], mix_only=True)
     fin = oracle.kawpow_hash_no_verify(bad_mix.height, bad_mix.kawpow_header_hash(), bad_mix.mix_hash[::-1], bad_mix.nonce64)
     assert got == [node.HEADER_OK if fin <= target else node.HEADER_HIGH_HASH, node.HEADER_OK]
+
+
+def test_external_miner_rpc_surface(nx, ctx_of, oracle):
+    """rpc/mining.cpp:722-737 (pprpcheader/pprpcepoch), :763-840 (getkawpowhash), :842-880 (pprpcsb's PoW gate):
+    a template goes out as header hash + epoch, an external miner answers with mix + nonce in hex, the node re-hashes."""
+    from nodexa_chain_core_b200 import node, progpow
+    k = golden("kawpow_kats.json")["hash_30000"]  # kawpow_tests.cpp:58-73, epoch 4
+    ctx = ctx_of(4)
+    r = node.getkawpowhash(ctx, k["header"], k["mix"], "%x" % k["nonce"], k["height"], target="0x" + k["final"])
+    assert r == {"result": "true", "digest": k["final"], "mix_hash": k["mix"], "info": "", "meets_target": "true"}
+    lower = "%064x" % (int(k["final"], 16) - 1)
+    r = node.getkawpowhash(ctx, k["header"], "00" + k["mix"][2:], "0x%x" % k["nonce"], k["height"], target=lower)
+    assert (r["result"], r["meets_target"], r["digest"]) == ("false", "false", k["final"])
+    assert "meets_target" not in node.getkawpowhash(ctx, k["header"], k["mix"], "%x" % k["nonce"], k["height"])
+    for bad in ("xyz", "1" * 17, "-1"):
+        with pytest.raises(ValueError):
+            node.getkawpowhash(ctx, k["header"], k["mix"], bad, k["height"])
+
+    ctx0 = ctx_of(0)
+    tmpl = node.BlockHeader(0x30000000, bytes(range(32)), bytes(range(32, 64)), node.MAINNET_KAWPOW_ACTIVATION_TIME + 5,
+                            0x2000ffff, 4242)
+    out = node.pprpc_fields(tmpl)
+    assert out == {"pprpcheader": oracle.kawpow_header_hash(tmpl.version, tmpl.prev_block, tmpl.merkle_root, tmpl.time,
+                                                             tmpl.bits, tmpl.height).hex(), "pprpcepoch": 0}
+    ok_t, target = oracle.compact_to_boundary(tmpl.bits)
+    sr = progpow.search(ctx0, tmpl.height, bytes.fromhex(out["pprpcheader"]), target, 0, 1 << 14)  # the external miner
+    assert sr.solution_found
+    accepted, filled = node.pprpcsb_check(ctx0, tmpl, sr.mix_hash.hex(), "%x" % sr.nonce)
+    assert accepted and node.check_block_headers(ctx0, [filled]) == [node.HEADER_OK]
+    # a nonce that does not solve the block is turned away ("Block does not solve the boundary")
+    miss = next(n for n in range(64) if oracle.kawpow_hash(0, tmpl.height, bytes.fromhex(out["pprpcheader"]), n)[0] > target)
+    accepted, _ = node.pprpcsb_check(ctx0, tmpl, sr.mix_hash.hex(), "%x" % miss)
+    assert not accepted
+    # the right nonce with somebody else's mix passes this gate (GetHashFull ignores the claim) and fails the next one
+    accepted, forged = node.pprpcsb_check(ctx0, tmpl, "ab" * 32, "%x" % sr.nonce)
+    assert accepted and node.check_block_headers(ctx0, [forged])[0] in (node.HEADER_INVALID_MIX, node.HEADER_HIGH_HASH)
