@@ -30,7 +30,8 @@ struct nx_miner
     std::vector<nx_epoch*> current;     // one per device
     int next_epoch = -1;
     std::vector<nx_epoch*> next;        // prebuilt contexts for next_epoch (may be empty)
-    std::future<int> background;
+    std::mutex bg_mu;                   // guards `background` itself (prepare_async may be called beside a search)
+    std::shared_future<int> background;
     uint64_t batch = 1ull << 22;
     // statistics of the last search
     std::atomic<uint64_t> hashes{0};
@@ -40,6 +41,12 @@ struct nx_miner
 
 namespace
 {
+std::shared_future<int> background_of(nx_miner* m)
+{
+    std::lock_guard<std::mutex> lk(m->bg_mu);
+    return m->background;
+}
+
 void destroy_all(std::vector<nx_epoch*>& v)
 {
     for (nx_epoch* c : v) nx_epoch_destroy(c);
@@ -156,7 +163,7 @@ static int nx_miner_create_body(const int* devices, int n_devices, nx_miner** ou
 void nx_miner_destroy(nx_miner* m)
 {
     if (!m) return;
-    if (m->background.valid()) m->background.wait();
+    if (auto bg = background_of(m); bg.valid()) bg.wait();
     destroy_all(m->current);
     destroy_all(m->next);
     delete m;
@@ -181,7 +188,15 @@ static int nx_miner_set_epoch_body(nx_miner* m, int epoch)
         set_error("bad argument");
         return NX_ERR_INVALID;
     }
-    if (m->background.valid()) m->background.wait();  // do not race the prebuild of the same epoch
+    {
+        // the common case - same epoch as last time - must not wait for a background task: that task may be the
+        // compilation of the NEXT period, which is meant to overlap the mining of this one
+        std::lock_guard<std::mutex> lk(m->mu);
+        if (m->epoch == epoch && !m->current.empty()) return NX_OK;
+    }
+    // an epoch switch replaces (and frees) the current contexts: let a background task that may be using them, or
+    // that may be building this very epoch, finish first
+    if (auto bg = background_of(m); bg.valid()) bg.wait();
     std::lock_guard<std::mutex> lk(m->mu);
     if (m->epoch == epoch && !m->current.empty()) return NX_OK;
     if (m->next_epoch == epoch && !m->next.empty()) {
@@ -209,6 +224,7 @@ static int nx_miner_prepare_async_body(nx_miner* m, int block_number, int lookah
         set_error("bad argument");
         return NX_ERR_INVALID;
     }
+    std::lock_guard<std::mutex> bg_lk(m->bg_mu);
     if (m->background.valid() &&
         m->background.wait_for(std::chrono::seconds(0)) != std::future_status::ready)
         return NX_OK;  // still busy with the previous request
@@ -251,8 +267,9 @@ static int nx_miner_prepare_async_body(nx_miner* m, int block_number, int lookah
 int nx_miner_wait_prepared(nx_miner* m)
 {
     if (!m) return NX_ERR_INVALID;
-    if (!m->background.valid()) return NX_OK;
-    return guarded([&] { return m->background.get(); });  // get() rethrows whatever the background task threw
+    const std::shared_future<int> bg = background_of(m);
+    if (!bg.valid()) return NX_OK;
+    return guarded([&] { return bg.get(); });  // get() rethrows whatever the background task threw
 }
 
 int nx_miner_epoch(const nx_miner* m) { return m ? m->epoch : -1; }

@@ -144,3 +144,28 @@ def test_program_cache_dir_persists_compiled_periods(tmp_path):
         import re
         return float(re.search(r": ([0-9.]+) ms, regs", stderr).group(1))
     assert compile_ms(second.stderr) < compile_ms(first.stderr)  # loading a cubin beats NVRTC
+
+
+def test_chain_across_period_switches_and_an_epoch_boundary(nx, oracle):
+    """Block after block like a node (tools/soak_chain.py): 24 linked blocks from height 7488 to 7511 - eight ProgPoW
+    periods, epoch 0 -> 1 with the next epoch prebuilt in the background - every header then passes the batched
+    CheckBlockHeader path and the oracle."""
+    import importlib.util
+    import os
+    from nodexa_chain_core_b200 import node
+    spec = importlib.util.spec_from_file_location("soak_chain", os.path.join(os.path.dirname(__file__), "..", "tools", "soak_chain.py"))
+    soak = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(soak)
+    headers, secs, _ = soak.mine_chain(nx, node, 7488, 24, 0x2000ffff, lookahead=6, devices=[0], batch=1 << 12)
+    assert [h.height for h, _ in headers] == list(range(7488, 7512))
+    for e in (0, 1):
+        ctx = nx.EpochContext(e, 0)
+        try:
+            hs = [h for h, _ in headers if h.height // 7500 == e]
+            assert len(hs) == 12 and node.check_block_headers(ctx, hs) == [node.HEADER_OK] * 12
+        finally:
+            ctx.close()
+    for (h, sr), (nxt, _) in zip(headers, headers[1:]):
+        assert nxt.prev_block == h.block_hash() == sr.final_hash[::-1]
+    for h, sr in headers[::5]:
+        assert oracle.kawpow_hash(h.height // 7500, h.height, h.kawpow_header_hash(), h.nonce64) == (sr.final_hash, sr.mix_hash)
