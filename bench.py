@@ -336,7 +336,7 @@ def main():
             "gpu_launches": args.steps + e2e_steps * ((B + (1 << 22) - 1) // (1 << 22)),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_hash": DAG_BYTES_PER_HASH, "kernel": "nx_kawpow_search_kernel",
+                         "algorithmic_bytes_per_hash": DAG_BYTES_PER_HASH, "kernel": "nx_kawpow_kernel (search mode)",
                          "roofline_mhs": peak * 1e9 / DAG_BYTES_PER_HASH / 1e6},
             "clocks": clocks,
             "found_nonce_plumbing": plumbing,

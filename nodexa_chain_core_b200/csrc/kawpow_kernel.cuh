@@ -225,6 +225,8 @@ struct NxJob
     u64 start_nonce;
     u64 count;           // nonces that may be reported; the grid is rounded up to whole CTAs
     u64 report_base;     // search mode reports report_base + (nonce - start_nonce)
+    u32 mode;            // 0: store {final, mix} per nonce;  1: search (compare on device, atomicMin the offset)
+    u32 pad;
 };
 
 NX_DEV u32 nx_bswap(u32 x) { return __byte_perm(x, 0, 0x0123); }
@@ -257,10 +259,11 @@ NX_DEV uint4 nx_ld_dag(const uint4* p)
     return v;
 }
 
-// MODE 0: store {final[8], mix[8]} per nonce.   MODE 1: atomicMin the offset of qualifying nonces.
-template <int MODE>
-NX_DEV void nx_kawpow_body(const uint4* __restrict__ dag, const NxJob& job, u32* __restrict__ out,
-                           u64* __restrict__ found_min)
+// One kernel for both uses, so that a period costs ONE NVRTC compilation: job.mode 0 stores {final[8], mix[8]} per
+// nonce into `result` (u32[16] each), job.mode 1 atomicMins the offset of qualifying nonces into `result` (one u64).
+// The mode only decides what happens to the finished hash - a uniform branch after the last keccak.
+extern "C" __global__ void __launch_bounds__(NX_THREADS, NX_MIN_BLOCKS)
+nx_kawpow_kernel(const uint4* __restrict__ dag, const NxJob job, void* __restrict__ result)
 {
     // dynamic shared memory: [L1 cache, NX_L1_COPIES interleaved replicas][carry 6 x T][digest 8 x T]
     extern __shared__ __align__(16) u32 nx_smem[];
@@ -348,8 +351,8 @@ NX_DEV void nx_kawpow_body(const uint4* __restrict__ dag, const NxJob& job, u32*
     nxk_f800(st);
 
     if (gid >= job.count) return;
-    if (MODE == 0) {
-        uint4* o = reinterpret_cast<uint4*>(out + gid * 16u);
+    if (job.mode == 0u) {
+        uint4* o = reinterpret_cast<uint4*>(static_cast<u32*>(result) + gid * 16u);
         o[0] = make_uint4(st[0], st[1], st[2], st[3]);
         o[1] = make_uint4(st[4], st[5], st[6], st[7]);
         o[2] = make_uint4(digest_s[0][tid], digest_s[1][tid], digest_s[2][tid], digest_s[3][tid]);
@@ -365,19 +368,7 @@ NX_DEV void nx_kawpow_body(const uint4* __restrict__ dag, const NxJob& job, u32*
                 break;
             }
         }
-        if (ok) atomicMin(found_min, job.report_base + gid);
+        if (ok) atomicMin(static_cast<u64*>(result), job.report_base + gid);
     }
-}
-
-extern "C" __global__ void __launch_bounds__(NX_THREADS, NX_MIN_BLOCKS)
-nx_kawpow_hash_kernel(const uint4* __restrict__ dag, const NxJob job, u32* __restrict__ out)
-{
-    nx_kawpow_body<0>(dag, job, out, nullptr);
-}
-
-extern "C" __global__ void __launch_bounds__(NX_THREADS, NX_MIN_BLOCKS)
-nx_kawpow_search_kernel(const uint4* __restrict__ dag, const NxJob job, u64* __restrict__ found_min)
-{
-    nx_kawpow_body<1>(dag, job, nullptr, found_min);
 }
 #endif  // __CUDACC__ && !NX_HELPERS_ONLY

@@ -555,10 +555,11 @@ int nx_kawpow_hash(const nx_epoch* c, int block_number, const uint8_t header_has
         set_error("null argument");
         return NX_ERR_INVALID;
     }
-    // A one-off hash (the node's verify path) does not wait for NVRTC: unless this period's program is
-    // already compiled, it goes through the interpreted kernel.
-    if (kawpow_program_is_cached(c->device, (uint64_t)(block_number / NX_PERIOD_LENGTH), c->dag_items) ||
-        block_number / NX_EPOCH_LENGTH != c->epoch) {
+    // A one-off hash (the node's verify path, the re-hash of a search hit) goes through the interpreted kernel K6:
+    // no NVRTC wait, and one half-warp finishes one nonce in 0.3 ms where the compiled kernel - whose threads each
+    // walk 16 nonce slots - needs a whole 0.8 ms wave.  Only a block outside this context's epoch (which K6's
+    // record check refuses) takes the compiled path, as the reference lets context and height disagree.
+    if (block_number / NX_EPOCH_LENGTH != c->epoch) {
         rc = nx_kawpow_hash_batch(c, block_number, header_hash, nonce, 1, buf);
     } else {
         nx_hash_record r;

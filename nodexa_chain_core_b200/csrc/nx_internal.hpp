@@ -74,6 +74,8 @@ struct KawpowJob
     uint64_t start_nonce;
     uint64_t count;
     uint64_t report_base;
+    uint32_t mode;  // 0 batch hash, 1 search (set by the launch helpers)
+    uint32_t pad;
 };
 struct KawpowProgram;  // one loaded module: (device, prog_seed, dag_items)
 int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items_256, std::shared_ptr<KawpowProgram>* out);

@@ -119,7 +119,7 @@ std::string cache_path(uint64_t prog_seed, uint32_t dag_items, const char* arch)
     const char* dir = std::getenv("NX_PROGRAM_CACHE_DIR");
     if (!dir || !*dir) return "";
     std::ostringstream s;
-    s << dir << "/kawpow_" << arch << "_" << prog_seed << "_" << dag_items << "_" << tune().tag() << "_v2.cubin";
+    s << dir << "/kawpow_" << arch << "_" << prog_seed << "_" << dag_items << "_" << tune().tag() << "_v3.cubin";
     return s.str();
 }
 }  // namespace
@@ -130,9 +130,9 @@ struct KawpowProgram
     uint64_t prog_seed = 0;
     uint32_t dag_items = 0;
     CUmodule_ module = nullptr;
-    CUfunction_ fn_hash = nullptr, fn_search = nullptr;
+    CUfunction_ fn = nullptr;  // nx_kawpow_kernel: batch hash and search are two modes of one kernel
     double compile_ms = 0;
-    int regs_hash = 0, regs_search = 0;
+    int regs = 0;
     int threads = 256;
     size_t smem_bytes = 0;
     ~KawpowProgram();
@@ -275,8 +275,7 @@ static int get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
         set_error("cuModuleLoadData failed: %s", cu_err(r));
         return NX_ERR_CUDA;
     }
-    if ((r = d.ModuleGetFunction(&p->fn_hash, p->module, "nx_kawpow_hash_kernel")) != 0 ||
-        (r = d.ModuleGetFunction(&p->fn_search, p->module, "nx_kawpow_search_kernel")) != 0) {
+    if ((r = d.ModuleGetFunction(&p->fn, p->module, "nx_kawpow_kernel")) != 0) {
         set_error("cuModuleGetFunction failed: %s", cu_err(r));
         return NX_ERR_CUDA;
     }
@@ -284,21 +283,16 @@ static int get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
     p->smem_bytes = tune().smem_bytes();
     if (p->smem_bytes > 48 * 1024) {
         if (!d.FuncSetAttribute ||
-            (r = d.FuncSetAttribute(p->fn_hash, 8 /*CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES*/, (int)p->smem_bytes)) != 0 ||
-            (r = d.FuncSetAttribute(p->fn_search, 8, (int)p->smem_bytes)) != 0) {
+            (r = d.FuncSetAttribute(p->fn, 8 /*CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES*/, (int)p->smem_bytes)) != 0) {
             set_error("cuFuncSetAttribute(max dynamic shared memory = %zu) failed: %s", p->smem_bytes, cu_err(r));
             return NX_ERR_CUDA;
         }
     }
-    if (d.FuncGetAttribute) {
-        d.FuncGetAttribute(&p->regs_hash, 4 /*CU_FUNC_ATTRIBUTE_NUM_REGS*/, p->fn_hash);
-        d.FuncGetAttribute(&p->regs_search, 4, p->fn_search);
-    }
+    if (d.FuncGetAttribute) d.FuncGetAttribute(&p->regs, 4 /*CU_FUNC_ATTRIBUTE_NUM_REGS*/, p->fn);
     p->compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (std::getenv("NX_VERBOSE"))
-        fprintf(stderr, "[nx] kawpow program seed=%llu items=%u tune=%s: %.1f ms, regs hash=%d search=%d smem=%zu\n",
-                (unsigned long long)prog_seed, dag_items, tune().tag().c_str(), p->compile_ms, p->regs_hash,
-                p->regs_search, p->smem_bytes);
+        fprintf(stderr, "[nx] kawpow program seed=%llu items=%u tune=%s: %.1f ms, regs=%d smem=%zu\n",
+                (unsigned long long)prog_seed, dag_items, tune().tag().c_str(), p->compile_ms, p->regs, p->smem_bytes);
     std::lock_guard<std::mutex> lk(g_cache_mu);
     auto it = g_cache.find(key);
     if (it != g_cache.end()) {  // another thread loaded the same program meanwhile: keep one
@@ -323,17 +317,20 @@ int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
     return guarded([&] { return get_program(device, prog_seed, dag_items, out); });
 }
 
-static int launch(const KawpowProgram* p, CUfunction_ fn, const void* dag, const KawpowJob& job, void* third,
+static int launch(const KawpowProgram* p, uint32_t mode, const void* dag, const KawpowJob& job_in, void* third,
                   cudaStream_t s)
 {
-    if (job.count == 0) return NX_OK;
+    if (job_in.count == 0) return NX_OK;
+    KawpowJob job = job_in;
+    job.mode = mode;
+    job.pad = 0;
     const uint64_t blocks = (job.count + p->threads - 1) / p->threads;
     if (blocks > 0x7fffffffull) {
         set_error("kawpow launch: batch of %llu nonces is too large for one grid", (unsigned long long)job.count);
         return NX_ERR_INVALID;
     }
     void* args[3] = {(void*)&dag, (void*)&job, (void*)&third};
-    const CUresult_ r = driver().LaunchKernel(fn, (unsigned)blocks, 1, 1, (unsigned)p->threads, 1, 1,
+    const CUresult_ r = driver().LaunchKernel(p->fn, (unsigned)blocks, 1, 1, (unsigned)p->threads, 1, 1,
                                               (unsigned)p->smem_bytes, (void*)s, args, nullptr);
     if (r != 0) {
         set_error("cuLaunchKernel failed: %s", cu_err(r));
@@ -344,12 +341,12 @@ static int launch(const KawpowProgram* p, CUfunction_ fn, const void* dag, const
 
 int kawpow_launch_hash(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* out_dev, cudaStream_t s)
 {
-    return launch(p, p->fn_hash, dag, job, out_dev, s);
+    return launch(p, 0u, dag, job, out_dev, s);
 }
 
 int kawpow_launch_search(const KawpowProgram* p, const void* dag, const KawpowJob& job, void* found_min_dev, cudaStream_t s)
 {
-    return launch(p, p->fn_search, dag, job, found_min_dev, s);
+    return launch(p, 1u, dag, job, found_min_dev, s);
 }
 
 }  // namespace nx

@@ -94,7 +94,7 @@ def test_nvrtc_compiles_for_sm100a_without_spills(nx, tmp_path):
     assert re.search(r"arch = sm_100a|EF_CUDA_SM100|sm_100", elf), elf[:400]
     out = subprocess.check_output([cuobjdump, "-res-usage", str(p)], text=True)
     usage = re.findall(r"Function (\w+):\s*\n\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", out)
-    assert {u[0] for u in usage} == {"nx_kawpow_hash_kernel", "nx_kawpow_search_kernel"}
+    assert {u[0] for u in usage} == {"nx_kawpow_kernel"}
     for name, reg, stack, shared, local in usage:
         assert int(reg) <= 64, (name, reg)
         assert int(stack) == 0 and int(local) == 0, (name, stack, local)
