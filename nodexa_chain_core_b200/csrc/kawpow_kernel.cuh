@@ -226,6 +226,8 @@ struct NxJob
     u64 count;           // nonces that may be reported; the grid is rounded up to whole CTAs
     u64 report_base;     // search mode reports report_base + (nonce - start_nonce)
     u32 mode;            // 0: store {final, mix} per nonce;  1: search (compare on device, atomicMin the offset)
+    u32 l1_mul_lo;       // 2^20                      } NX_L1_HI == 2: L1 addressing multipliers handed over as kernel
+    u32 l1_mul_hi;       // 2^(14 + log2 L1 replicas) } parameters, so that ptxas cannot fold the multiplies into ALU shifts
     u32 pad;
 };
 
@@ -235,10 +237,15 @@ NX_DEV u32 nx_bswap(u32 x) { return __byte_perm(x, 0, 0x0123); }
 //   default:    AND (ALU pipe) + multiply-add (FMA pipe) + LDS
 //   NX_L1_HI:   x*2^20 keeps only the low 12 bits of x; the high half of (that * 2^(14+log2 copies)) is the
 //               scaled index, so both steps run on the FMA pipe and the ALU pipe (the busier one) is spared.
-NX_DEV u32 nx_l1_load(u32 x, u32 lane_base)
+NX_DEV u32 nx_l1_load(u32 x, u32 lane_base, u32 mul_lo, u32 mul_hi)
 {
     u32 v;
-#if NX_L1_HI
+#if NX_L1_HI == 2
+    // both multipliers are kernel parameters (constant-bank operands): two FMA-pipe multiplies, no ALU-pipe work
+    asm("{\n\t.reg .u32 t;\n\tmul.lo.u32 t, %1, %2;\n\tmad.hi.u32 t, t, %3, %4;\n\tld.shared.u32 %0, [t];\n\t}"
+        : "=r"(v)
+        : "r"(x), "r"(mul_lo), "r"(mul_hi), "r"(lane_base));
+#elif NX_L1_HI
     asm("{\n\t.reg .u32 t;\n\tmul.lo.u32 t, %1, 1048576;\n\tmad.hi.u32 t, t, %2, %3;\n\tld.shared.u32 %0, [t];\n\t}"
         : "=r"(v)
         : "r"(x), "n"(1 << (14 + NX_L1_LOG)), "r"(lane_base));
@@ -320,7 +327,7 @@ nx_kawpow_kernel(const uint4* __restrict__ dag, const NxJob job, void* __restric
             // item index comes from lane r%16 (reference progpow.cpp:182-183)
             const u32 item = __shfl_sync(0xffffffffu, m[0], r & 15u, 16) % NX_DAG_ITEMS;
             const uint4 d = nx_ld_dag(dag + ((u64)item * 16u + ((lane ^ r) & 15u)));
-#define NX_L1(x) nx_l1_load((x), l1_base)
+#define NX_L1(x) nx_l1_load((x), l1_base, job.l1_mul_lo, job.l1_mul_hi)
             NX_ROUND_CACHE_MATH(m, NX_L1);
 #undef NX_L1
             NX_ROUND_DAG(m, d.x, d.y, d.z, d.w);

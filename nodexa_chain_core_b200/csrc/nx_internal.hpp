@@ -75,6 +75,7 @@ struct KawpowJob
     uint64_t count;
     uint64_t report_base;
     uint32_t mode;  // 0 batch hash, 1 search (set by the launch helpers)
+    uint32_t l1_mul_lo, l1_mul_hi;  // L1 addressing multipliers for the NX_L1_HI == 2 shape (set by the launch helpers)
     uint32_t pad;
 };
 struct KawpowProgram;  // one loaded module: (device, prog_seed, dag_items)

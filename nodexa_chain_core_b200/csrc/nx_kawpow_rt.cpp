@@ -105,7 +105,7 @@ const Tune& tune()
                 if (k == "threads" && v >= 32 && v <= 1024 && v % 32 == 0) t.threads = v;
                 if (k == "minblocks" && v >= 1 && v <= 8) t.minblocks = v;
                 if (k == "rotimad" && v >= 0 && v <= 16) t.rotimad = v;
-                if (k == "l1hi") t.l1hi = v ? 1 : 0;
+                if (k == "l1hi" && v >= 0 && v <= 2) t.l1hi = v;
                 if (k == "unroll" && (v == 1 || v == 2 || v == 4 || v == 8)) t.unroll = v;
             }
             pos = end + 1;
@@ -323,6 +323,10 @@ static int launch(const KawpowProgram* p, uint32_t mode, const void* dag, const 
     if (job_in.count == 0) return NX_OK;
     KawpowJob job = job_in;
     job.mode = mode;
+    int log_copies = 0;
+    while ((1 << log_copies) < tune().copies) ++log_copies;
+    job.l1_mul_lo = 1u << 20;
+    job.l1_mul_hi = 1u << (14 + log_copies);
     job.pad = 0;
     const uint64_t blocks = (job.count + p->threads - 1) / p->threads;
     if (blocks > 0x7fffffffull) {
