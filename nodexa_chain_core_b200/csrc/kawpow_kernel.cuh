@@ -50,6 +50,9 @@ typedef unsigned long long u64;
 #ifndef NX_ROT_IMAD
 #define NX_ROT_IMAD 0
 #endif
+#ifndef NX_ILV
+#define NX_ILV 1  // nonces a half-warp works on at the same time (1 or 2)
+#endif
 #ifndef NX_L1_HI
 #define NX_L1_HI 0
 #endif
@@ -317,33 +320,67 @@ nx_kawpow_kernel(const uint4* __restrict__ dag, const NxJob job, void* __restric
     }
     __syncthreads();
 
+    // NX_ILV == 2: the half-warp walks its 16 nonces two at a time, both mixes (2 x 32 words) live in registers and the
+    // two round programs are independent instruction streams.  A hash is a chain of 64 dependent DAG reads (each round's
+    // item index comes out of the previous round's DAG merge), so what one SM delivers is (hashes in flight) / (64 x
+    // DRAM latency); two hashes per thread share the non-mix registers and so put more hashes in flight per register file.
 #pragma unroll 1
-    for (u32 h = 0; h < 16u; ++h) {
+    for (u32 h = 0; h < 16u; h += NX_ILV) {
         u32 m[32];
         nx_fill_mix(__shfl_sync(0xffffffffu, seed0, h, 16), __shfl_sync(0xffffffffu, seed1, h, 16), lane, m);
+#if NX_ILV == 2
+        u32 n[32];
+        nx_fill_mix(__shfl_sync(0xffffffffu, seed0, h + 1u, 16), __shfl_sync(0xffffffffu, seed1, h + 1u, 16), lane, n);
+#endif
 
 #pragma unroll NX_UNROLL
         for (u32 r = 0; r < 64u; ++r) {
             // item index comes from lane r%16 (reference progpow.cpp:182-183)
             const u32 item = __shfl_sync(0xffffffffu, m[0], r & 15u, 16) % NX_DAG_ITEMS;
             const uint4 d = nx_ld_dag(dag + ((u64)item * 16u + ((lane ^ r) & 15u)));
+#if NX_ILV == 2
+            const u32 item2 = __shfl_sync(0xffffffffu, n[0], r & 15u, 16) % NX_DAG_ITEMS;
+            const uint4 e = nx_ld_dag(dag + ((u64)item2 * 16u + ((lane ^ r) & 15u)));
+#endif
 #define NX_L1(x) nx_l1_load((x), l1_base, job.l1_mul_lo, job.l1_mul_hi)
             NX_ROUND_CACHE_MATH(m, NX_L1);
+#if NX_ILV == 2
+            NX_ROUND_CACHE_MATH(n, NX_L1);
+#endif
 #undef NX_L1
             NX_ROUND_DAG(m, d.x, d.y, d.z, d.w);
+#if NX_ILV == 2
+            NX_ROUND_DAG(n, e.x, e.y, e.z, e.w);
+#endif
         }
 
         // 16 lane hashes -> 8 words (reference progpow.cpp:288-293)
-        const u32 lh = nx_lane_reduce(m);
-        u32 dg[8];
+        {
+            const u32 lh = nx_lane_reduce(m);
+            u32 dg[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-            dg[i] = nx_fnv1a(nx_fnv1a(NX_FNV_BASIS, __shfl_sync(0xffffffffu, lh, i, 16)),
-                             __shfl_sync(0xffffffffu, lh, i + 8, 16));
-        if (h == lane) {
+            for (int i = 0; i < 8; ++i)
+                dg[i] = nx_fnv1a(nx_fnv1a(NX_FNV_BASIS, __shfl_sync(0xffffffffu, lh, i, 16)),
+                                 __shfl_sync(0xffffffffu, lh, i + 8, 16));
+            if (h == lane) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) digest_s[i][tid] = dg[i];
+                for (int i = 0; i < 8; ++i) digest_s[i][tid] = dg[i];
+            }
         }
+#if NX_ILV == 2
+        {
+            const u32 lh = nx_lane_reduce(n);
+            u32 dg[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                dg[i] = nx_fnv1a(nx_fnv1a(NX_FNV_BASIS, __shfl_sync(0xffffffffu, lh, i, 16)),
+                                 __shfl_sync(0xffffffffu, lh, i + 8, 16));
+            if (h + 1u == lane) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) digest_s[i][tid] = dg[i];
+            }
+        }
+#endif
     }
     // digest_s[.][tid] was written by this very thread: no barrier needed
 
