@@ -296,6 +296,44 @@ enum
 int nx_check_block_headers(const nx_epoch* ctx, const uint8_t* raw_headers /* n x 120 */, size_t n,
                            const uint8_t pow_limit_be[32], int mix_only, uint8_t* status);
 
+/* Block-index records as the node keeps them in LevelDB: CDiskBlockIndex::SerializationOp (chain.h:398-431) over the
+ * VARINT coding of serialize.h:290-366.  Record = VARINT client version | VARINT nHeight | VARINT nStatus | VARINT nTx |
+ * [VARINT nFile if status has DATA or UNDO] | [VARINT nDataPos if DATA] | [VARINT nUndoPos if UNDO] | nVersion i32 |
+ * hashPrev[32] | hashMerkleRoot[32] | nTime u32 | nBits u32 | then nNonce u32 for blocks before the KawPow activation
+ * time, else nNonce64 u64 | mix_hash[32].  (nHeight is NOT repeated in the header part.)  Host only. */
+#define NX_BLOCK_HAVE_DATA 8u  /* chain.h:156 */
+#define NX_BLOCK_HAVE_UNDO 16u /* chain.h:157 */
+typedef struct nx_disk_block_index
+{
+    int32_t client_version;
+    int32_t height;
+    uint32_t status;
+    uint32_t tx_count;
+    int32_t file;
+    uint32_t data_pos;
+    uint32_t undo_pos;
+    int32_t version;
+    uint8_t prev_block[32]; /* uint256 storage order */
+    uint8_t merkle_root[32];
+    uint32_t time;
+    uint32_t bits;
+    uint32_t nonce;       /* blocks before the activation time */
+    uint64_t nonce64;     /* KawPow blocks */
+    uint8_t mix_hash[32]; /* KawPow blocks, uint256 storage order */
+} nx_disk_block_index;
+/* WriteVarInt / ReadVarInt<uint64_t>: bytes written (1..10) / bytes consumed, 0 for a truncated or oversized number. */
+size_t nx_varint_write(uint64_t n, uint8_t out[10]);
+size_t nx_varint_read(const uint8_t* in, size_t len, uint64_t* n);
+/* Bytes written, 0 when `cap` is too small or a signed field is negative. */
+size_t nx_disk_block_index_serialize(const nx_disk_block_index* in, uint32_t kawpow_activation_time, uint8_t* out, size_t cap);
+/* Bytes consumed, 0 for a malformed record (truncated, or a VARINT beyond its field's type - where ReadVarInt throws). */
+size_t nx_disk_block_index_parse(const uint8_t* in, size_t len, uint32_t kawpow_activation_time, nx_disk_block_index* out);
+/* The check LoadBlockIndexGuts makes on every record at start-up (txdb.cpp:470-492): rebuild the header, take
+ * GetBlockHash() - for a KawPow block the mix-only hash - and CheckProofOfWork it against nBits.  Returns 1 / 0, or -1 for
+ * a block before the activation time (X16R: not this library's).  block_id (may be NULL) receives GetBlockHash(). */
+int nx_disk_block_index_check(const nx_disk_block_index* rec, uint32_t kawpow_activation_time, const uint8_t pow_limit_be[32],
+                              uint8_t block_id_uint256[32]);
+
 /* ------------------------------------------------------------------------------------------------
  * Miner: one process, all GPUs.  Replaces the nonce loops of miner.cpp:656-713 (CloreMiner) and
  * rpc/mining.cpp:117-173 (generateBlocks), and the epoch-context handling of hash.cpp:260-266 /

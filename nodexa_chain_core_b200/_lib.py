@@ -40,6 +40,13 @@ class NxBlockHeader(C.Structure):
                 ("mix_hash", C.c_uint8 * 32)]
 
 
+class NxDiskBlockIndex(C.Structure):
+    _fields_ = [("client_version", C.c_int32), ("height", C.c_int32), ("status", C.c_uint32), ("tx_count", C.c_uint32),
+                ("file", C.c_int32), ("data_pos", C.c_uint32), ("undo_pos", C.c_uint32), ("version", C.c_int32),
+                ("prev_block", C.c_uint8 * 32), ("merkle_root", C.c_uint8 * 32), ("time", C.c_uint32), ("bits", C.c_uint32),
+                ("nonce", C.c_uint32), ("nonce64", C.c_uint64), ("mix_hash", C.c_uint8 * 32)]
+
+
 class NxVerifyRecord(C.Structure):
     _fields_ = [("block_number", C.c_int32), ("pad", C.c_uint32), ("nonce", C.c_uint64),
                 ("header_hash", C.c_uint8 * 32), ("mix_hash", C.c_uint8 * 32), ("boundary", C.c_uint8 * 32)]
@@ -112,6 +119,11 @@ def _load() -> C.CDLL:
         "nx_block_header_serialize": (None, [C.POINTER(NxBlockHeader), u8p]),
         "nx_block_hash": (None, [u8p, u8p]),
         "nx_check_block_headers": (i, [vp, u8p, sz, u8p, i, u8p]),
+        "nx_varint_write": (sz, [u64, u8p]),
+        "nx_varint_read": (sz, [u8p, sz, C.POINTER(u64)]),
+        "nx_disk_block_index_serialize": (sz, [C.POINTER(NxDiskBlockIndex), u32, u8p, sz]),
+        "nx_disk_block_index_parse": (sz, [u8p, sz, u32, C.POINTER(NxDiskBlockIndex)]),
+        "nx_disk_block_index_check": (i, [C.POINTER(NxDiskBlockIndex), u32, u8p, u8p]),
         "nx_miner_create": (i, [C.POINTER(i), i, C.POINTER(vp)]),
         "nx_miner_destroy": (None, [vp]),
         "nx_miner_device_count": (i, [vp]),

@@ -338,6 +338,151 @@ void nx_block_hash(const uint8_t raw[120], uint8_t out_uint256[32])
     for (int i = 0; i < 32; ++i) out_uint256[i] = fin[31 - i];
 }
 
+// ---- block-index records (chain.h:398-431) over VARINT (serialize.h:290-366) ----
+size_t nx_varint_write(uint64_t n, uint8_t out[10])
+{
+    // MSB base-128, one subtracted from every digit but the last so that each number has exactly one encoding
+    uint8_t tmp[10];
+    int len = 0;
+    for (;;) {
+        tmp[len] = (uint8_t)((n & 0x7f) | (len ? 0x80 : 0x00));
+        if (n <= 0x7f) break;
+        n = (n >> 7) - 1;
+        ++len;
+    }
+    size_t w = 0;
+    do {
+        out[w++] = tmp[len];
+    } while (len--);
+    return w;
+}
+
+namespace
+{
+// ReadVarInt<I> with I's maximum passed in: the reference throws where this returns 0
+size_t varint_read_max(const uint8_t* in, size_t len, uint64_t max, uint64_t* out)
+{
+    uint64_t n = 0;
+    for (size_t i = 0; i < len; ++i) {
+        const uint8_t c = in[i];
+        if (n > (max >> 7)) return 0;
+        n = (n << 7) | (c & 0x7f);
+        if (c & 0x80) {
+            if (n == max) return 0;
+            ++n;
+        } else {
+            *out = n;
+            return i + 1;
+        }
+    }
+    return 0;  // ran out of input
+}
+constexpr uint64_t MAX_I32 = 0x7fffffffull, MAX_U32 = 0xffffffffull;
+}  // namespace
+
+size_t nx_varint_read(const uint8_t* in, size_t len, uint64_t* n)
+{
+    if (!in || !n) return 0;
+    return varint_read_max(in, len, ~0ull, n);
+}
+
+size_t nx_disk_block_index_serialize(const nx_disk_block_index* r, uint32_t activation, uint8_t* out, size_t cap)
+{
+    if (!r || !out || r->client_version < 0 || r->height < 0 || r->file < 0) return 0;
+    uint8_t buf[7 * 10 + 4 + 32 + 32 + 4 + 4 + 8 + 32];
+    size_t w = 0;
+    w += nx_varint_write((uint64_t)r->client_version, buf + w);
+    w += nx_varint_write((uint64_t)r->height, buf + w);
+    w += nx_varint_write(r->status, buf + w);
+    w += nx_varint_write(r->tx_count, buf + w);
+    if (r->status & (NX_BLOCK_HAVE_DATA | NX_BLOCK_HAVE_UNDO)) w += nx_varint_write((uint64_t)r->file, buf + w);
+    if (r->status & NX_BLOCK_HAVE_DATA) w += nx_varint_write(r->data_pos, buf + w);
+    if (r->status & NX_BLOCK_HAVE_UNDO) w += nx_varint_write(r->undo_pos, buf + w);
+    std::memcpy(buf + w, &r->version, 4); w += 4;
+    std::memcpy(buf + w, r->prev_block, 32); w += 32;
+    std::memcpy(buf + w, r->merkle_root, 32); w += 32;
+    std::memcpy(buf + w, &r->time, 4); w += 4;
+    std::memcpy(buf + w, &r->bits, 4); w += 4;
+    if (r->time < activation) {
+        std::memcpy(buf + w, &r->nonce, 4); w += 4;
+    } else {
+        std::memcpy(buf + w, &r->nonce64, 8); w += 8;
+        std::memcpy(buf + w, r->mix_hash, 32); w += 32;
+    }
+    if (w > cap) return 0;
+    std::memcpy(out, buf, w);
+    return w;
+}
+
+size_t nx_disk_block_index_parse(const uint8_t* in, size_t len, uint32_t activation, nx_disk_block_index* r)
+{
+    if (!in || !r) return 0;
+    std::memset(r, 0, sizeof *r);
+    size_t p = 0;
+    uint64_t v = 0;
+    auto take = [&](uint64_t max) -> bool {
+        const size_t used = varint_read_max(in + p, len - p, max, &v);
+        p += used;
+        return used != 0;
+    };
+    if (!take(MAX_I32)) return 0;
+    r->client_version = (int32_t)v;
+    if (!take(MAX_I32)) return 0;
+    r->height = (int32_t)v;
+    if (!take(MAX_U32)) return 0;
+    r->status = (uint32_t)v;
+    if (!take(MAX_U32)) return 0;
+    r->tx_count = (uint32_t)v;
+    if (r->status & (NX_BLOCK_HAVE_DATA | NX_BLOCK_HAVE_UNDO)) {
+        if (!take(MAX_I32)) return 0;
+        r->file = (int32_t)v;
+    }
+    if (r->status & NX_BLOCK_HAVE_DATA) {
+        if (!take(MAX_U32)) return 0;
+        r->data_pos = (uint32_t)v;
+    }
+    if (r->status & NX_BLOCK_HAVE_UNDO) {
+        if (!take(MAX_U32)) return 0;
+        r->undo_pos = (uint32_t)v;
+    }
+    auto fixed = [&](void* dst, size_t n) -> bool {
+        if (len - p < n) return false;
+        std::memcpy(dst, in + p, n);
+        p += n;
+        return true;
+    };
+    if (!fixed(&r->version, 4) || !fixed(r->prev_block, 32) || !fixed(r->merkle_root, 32) || !fixed(&r->time, 4) ||
+        !fixed(&r->bits, 4))
+        return 0;
+    if (r->time < activation) {
+        if (!fixed(&r->nonce, 4)) return 0;
+    } else {
+        if (!fixed(&r->nonce64, 8) || !fixed(r->mix_hash, 32)) return 0;
+    }
+    return p;
+}
+
+int nx_disk_block_index_check(const nx_disk_block_index* r, uint32_t activation, const uint8_t pow_limit_be[32], uint8_t block_id[32])
+{
+    if (!r) return 0;
+    if (r->time < activation) return -1;
+    nx_block_header h;
+    h.version = r->version;
+    std::memcpy(h.prev_block, r->prev_block, 32);
+    std::memcpy(h.merkle_root, r->merkle_root, 32);
+    h.time = r->time;
+    h.bits = r->bits;
+    h.height = (uint32_t)r->height;
+    h.nonce64 = r->nonce64;
+    std::memcpy(h.mix_hash, r->mix_hash, 32);
+    uint8_t raw[120], id[32], fin[32];
+    nx_block_header_serialize(&h, raw);
+    nx_block_hash(raw, id);
+    if (block_id) std::memcpy(block_id, id, 32);
+    for (int i = 0; i < 32; ++i) fin[i] = id[31 - i];
+    return nx_check_proof_of_work(fin, r->bits, pow_limit_be);
+}
+
 int nx_compact_to_boundary(uint32_t bits, uint8_t out[32])
 {
     const int size = (int)(bits >> 24);

@@ -7,7 +7,7 @@ import ctypes as C
 import struct
 from dataclasses import dataclass
 
-from ._lib import check, inb, lib, outb
+from ._lib import NxDiskBlockIndex, check, inb, lib, outb
 from .ethash import EpochContext
 
 HEADER_OK, HEADER_HIGH_HASH, HEADER_INVALID_MIX, HEADER_BAD_BITS, HEADER_WRONG_EPOCH = range(5)
@@ -47,6 +47,75 @@ class BlockHeader:
         o = outb(32)
         lib.nx_block_hash(inb(self.serialize()), o)
         return bytes(o)
+
+
+BLOCK_HAVE_DATA, BLOCK_HAVE_UNDO = 8, 16  # chain.h:156-157
+
+
+def varint_write(n: int) -> bytes:
+    """WriteVarInt (serialize.h:330-345)."""
+    o = outb(10)
+    return bytes(o[:lib.nx_varint_write(n, o)])
+
+
+def varint_read(data: bytes):
+    """ReadVarInt<uint64_t> (serialize.h:347-366): (value, bytes consumed); raises where the reference throws."""
+    v = C.c_uint64()
+    used = lib.nx_varint_read(inb(data) if data else outb(1), len(data), C.byref(v))
+    if not used:
+        raise ValueError("ReadVarInt(): size too large or truncated input")
+    return v.value, used
+
+
+@dataclass
+class DiskBlockIndex:
+    """One block-index record as LevelDB holds it (CDiskBlockIndex, chain.h:388-431)."""
+    client_version: int
+    height: int
+    status: int
+    tx_count: int
+    file: int = 0
+    data_pos: int = 0
+    undo_pos: int = 0
+    version: int = 0
+    prev_block: bytes = bytes(32)
+    merkle_root: bytes = bytes(32)
+    time: int = 0
+    bits: int = 0
+    nonce: int = 0
+    nonce64: int = 0
+    mix_hash: bytes = bytes(32)
+
+    def _c(self) -> NxDiskBlockIndex:
+        return NxDiskBlockIndex(self.client_version, self.height, self.status, self.tx_count, self.file, self.data_pos,
+                                self.undo_pos, self.version, (C.c_uint8 * 32)(*self.prev_block),
+                                (C.c_uint8 * 32)(*self.merkle_root), self.time, self.bits, self.nonce, self.nonce64,
+                                (C.c_uint8 * 32)(*self.mix_hash))
+
+    def serialize(self, kawpow_activation_time: int = MAINNET_KAWPOW_ACTIVATION_TIME) -> bytes:
+        o = outb(256)
+        n = lib.nx_disk_block_index_serialize(C.byref(self._c()), kawpow_activation_time, o, len(o))
+        if not n:
+            raise ValueError("record cannot be serialized (negative height/file/version)")
+        return bytes(o[:n])
+
+    @staticmethod
+    def parse(data: bytes, kawpow_activation_time: int = MAINNET_KAWPOW_ACTIVATION_TIME):
+        """Returns (record, bytes consumed); raises ValueError for a malformed record."""
+        r = NxDiskBlockIndex()
+        used = lib.nx_disk_block_index_parse(inb(data) if data else outb(1), len(data), kawpow_activation_time, C.byref(r))
+        if not used:
+            raise ValueError("malformed CDiskBlockIndex record")
+        return DiskBlockIndex(r.client_version, r.height, r.status, r.tx_count, r.file, r.data_pos, r.undo_pos, r.version,
+                              bytes(r.prev_block), bytes(r.merkle_root), r.time, r.bits, r.nonce, r.nonce64,
+                              bytes(r.mix_hash)), used
+
+    def check(self, kawpow_activation_time: int = MAINNET_KAWPOW_ACTIVATION_TIME, pow_limit: bytes = KAWPOW_LIMIT):
+        """LoadBlockIndexGuts's start-up check (txdb.cpp:470-492): (verdict, block id); verdict 1 ok, 0 PoW fails,
+        -1 pre-KawPow block (X16R, not this library's)."""
+        o = outb(32)
+        v = lib.nx_disk_block_index_check(C.byref(self._c()), kawpow_activation_time, inb(pow_limit), o)
+        return v, bytes(o)
 
 
 def compact_to_boundary(bits: int):

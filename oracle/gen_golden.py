@@ -164,6 +164,116 @@ def gen_epoch448(ref):
     write("misc.json", misc)
 
 
+def gen_node(_ref):
+    """Node-side glue from the reference's own block.cpp / hash.cpp / arith_uint256.cpp / chain.h (oracle/ref_node_shim.cpp)."""
+    from oracle.oracle import RefNode
+    rn = RefNode(MAINNET_KAWPOW_TIME)
+    rng = np.random.default_rng(20261107)
+    rb = lambda n: rng.bytes(n)  # noqa: E731
+    out = {"activation_time": MAINNET_KAWPOW_TIME, "client_version": rn.client_version(), "headers": [], "kawpow_hash": [],
+           "pre_activation_headers": [], "compact": [], "check_pow": [], "hex": [], "varint": [], "varint_bad": [],
+           "disk_index": [], "disk_index_bad": []}
+
+    def hdr_dict(f):
+        return {"version": f.version, "prev_block": bytes(f.prev_block).hex(), "merkle_root": bytes(f.merkle_root).hex(),
+                "time": f.time, "bits": f.bits, "nonce": f.nonce, "height": f.height, "nonce64": f.nonce64,
+                "mix_hash": bytes(f.mix_hash).hex()}
+
+    for i in range(12):
+        f = rn.fields(int(rng.integers(-2**31, 2**31)) if i else 0x30000000, rb(32), rb(32),
+                      MAINNET_KAWPOW_TIME + int(rng.integers(0, 10**8)), int(rng.integers(0, 2**32)), int(rng.integers(0, 2**31)),
+                      int(rng.integers(0, 2**64, dtype=np.uint64)), rb(32))
+        raw_hash, pp = rn.header_hash(f)
+        d = hdr_dict(f)
+        d.update(header_hash_uint256=raw_hash.hex(), header_hash_progpow=pp.hex(), kawpow_input=rn.kawpow_input(f).hex(),
+                 wire=rn.serialize_header(f).hex(), block_hash=rn.block_hash(f).hex())
+        pf, used = rn.parse_header(bytes.fromhex(d["wire"]))
+        assert used == 120 and hdr_dict(pf) == {**hdr_dict(f), "nonce": 0}
+        out["headers"].append(d)
+    for height in (0, 1234, 7499, 7500):  # KAWPOWHash builds a light context per epoch (two epochs here)
+        f = rn.fields(0x30000000, rb(32), rb(32), MAINNET_KAWPOW_TIME + 60 * height, 0x1e00ffff, height,
+                      int(rng.integers(0, 2**64, dtype=np.uint64)), bytes(32))
+        fin, mix = rn.kawpow_hash(f)
+        fin2, mix2 = rn.block_hash_full(f)
+        assert (fin, mix) == (fin2, mix2)
+        d = hdr_dict(f)
+        d.update(final_uint256=fin.hex(), mix_uint256=mix.hex())
+        # with the right mix in the header, GetHash() (mix-only) equals the full hash
+        g = rn.fields(f.version, bytes(f.prev_block), bytes(f.merkle_root), f.time, f.bits, f.height, f.nonce64, mix)
+        assert rn.block_hash(g) == fin
+        out["kawpow_hash"].append(d)
+    for i in range(3):  # 80-byte wire form of the X16R era: only the serialization is on this path
+        f = rn.fields(0x20000000, rb(32), rb(32), MAINNET_KAWPOW_TIME - 1 - i * 1000, 0x1c0fffff, 0, 0, bytes(32),
+                      nonce=int(rng.integers(0, 2**32)))
+        d = hdr_dict(f)
+        d["wire"] = rn.serialize_header(f).hex()
+        assert len(d["wire"]) == 160
+        out["pre_activation_headers"].append(d)
+    edge_bits = [0, 0x00123456, 0x01003456, 0x01123456, 0x01803456, 0x01fedcba, 0x02000056, 0x02008000, 0x02800056, 0x03000000,
+                 0x03123456, 0x03800000, 0x04000000, 0x04123456, 0x04800000, 0x04923456, 0x05009234, 0x1b0404cb, 0x1c0fffff,
+                 0x1d00ffff, 0x1e00ffff, 0x1f00ffff, 0x2000ffff, 0x20123456, 0x207fffff, 0x20800000, 0x21000001, 0x2100ffff,
+                 0x21010000, 0x22000001, 0x220000ff, 0x22000100, 0x23000001, 0xff123456, 0xffffffff]
+    for bits in edge_bits + [int(x) for x in rng.integers(0, 2**32, 40)]:
+        v, neg, ovf = rn.set_compact(bits)
+        out["compact"].append({"bits": bits, "value_be": v.hex(), "negative": neg, "overflow": ovf, "get_compact": rn.get_compact(v)})
+    limit_raw = bytes.fromhex("00" + "ff" * 31)[::-1]  # kawpowLimit (chainparams.cpp:116-117) as uint256 storage bytes
+    regtest_raw = bytes.fromhex("7f" + "ff" * 31)[::-1]
+    for bits in (0x1b0404cb, 0x1f00ffff, 0x2000ffff, 0x207fffff, 0x01803456, 0, 0x23000001):
+        target, _, _ = rn.set_compact(bits)
+        t = int.from_bytes(target, "big")
+        cands = [0, 1, max(t - 1, 0), t, t + 1, 2**256 - 1] + [int.from_bytes(rb(32), "big") >> int(rng.integers(0, 64)) for _ in range(4)]
+        for hv in cands:
+            hv %= 2**256
+            hraw = hv.to_bytes(32, "big")[::-1]
+            for lim_name, lim in (("main", limit_raw), ("regtest", regtest_raw)):
+                out["check_pow"].append({"hash_uint256": hraw.hex(), "bits": bits, "limit": lim_name, "ok": rn.check_pow(hraw, bits, lim)})
+    for _ in range(4):
+        raw = rb(32)
+        out["hex"].append({"raw": raw.hex(), "gethex": rn.get_hex(raw)})
+    for text in ("0x1234", "  abcdef", "00" * 31 + "7f", "ff" * 40, "12xyz"):
+        out["hex"].append({"sethex": text, "raw": rn.set_hex(text).hex()})
+    for n in [0, 1, 127, 128, 255, 256, 16383, 16384, 16511, 16512, 65535, 2113663, 2113664, 2**31 - 1, 2**31, 2**32 - 1, 2**32,
+              2**63, 2**64 - 1] + [int(x) for x in rng.integers(0, 2**63, 12)]:
+        enc = rn.write_varint(n)
+        assert rn.read_varint(enc) == (n, len(enc))
+        out["varint"].append({"n": str(n), "bytes": enc.hex()})
+    for bad in ("", "80", "ffff", "ff" * 10 + "00", "80" * 11, "fefefefefefefefefeff7f"):
+        v, used = rn.read_varint(bytes.fromhex(bad))
+        out["varint_bad"].append({"bytes": bad, "throws": used < 0, "value": None if used < 0 else str(v)})
+    statuses = [0, 1, 5, 8 | 3, 16 | 4, 8 | 16 | 5, 8 | 16 | 32 | 5, 0x80 | 8 | 5]
+    for i, st in enumerate(statuses + statuses[:3]):
+        pre = i >= len(statuses)
+        t = MAINNET_KAWPOW_TIME - 100 - i if pre else MAINNET_KAWPOW_TIME + int(rng.integers(0, 10**8))
+        f = rn.fields(0x30000000, rb(32), rb(32), t, int(rng.integers(0, 2**32)), 0,
+                      0 if pre else int(rng.integers(0, 2**64, dtype=np.uint64)), bytes(32) if pre else rb(32),
+                      nonce=int(rng.integers(0, 2**32)) if pre else 0)
+        height, ntx = int(rng.integers(0, 2**31)), int(rng.integers(0, 2**20))
+        file_, dpos, upos = int(rng.integers(0, 5000)), int(rng.integers(0, 2**32)), int(rng.integers(0, 2**32))
+        raw = rn.diskindex_serialize(height, st, ntx, file_, dpos, upos, f)
+        rec, cv, bh, used = rn.diskindex_parse(raw)
+        assert used == len(raw) and cv == rn.client_version()
+        rec = {k: (v.hex() if isinstance(v, bytes) else v) for k, v in rec.items()}
+        out["disk_index"].append({"raw": raw.hex(), "record": rec, "client_version": cv,
+                                  "block_hash": bh.hex() if bh is not None else None,
+                                  "pow_ok_main": None if bh is None else rn.check_pow(bh, f.bits, limit_raw)})
+    good = bytes.fromhex(out["disk_index"][5]["raw"])
+    big_height = rn.write_varint(4040402) + rn.write_varint(2**31) + good[6:]  # nHeight is an int: 2^31 does not fit
+    tail = struct.pack("<i32s32sIIQ32s", 1, rb(32), rb(32), MAINNET_KAWPOW_TIME + 1, 0x1b0404cb, 7, rb(32))
+
+    def scratch(cv, h, st, ntx, extra=b""):
+        return rn.write_varint(cv) + rn.write_varint(h) + rn.write_varint(st) + rn.write_varint(ntx) + extra + tail
+
+    limits = [scratch(4040402, 2**31 - 1, 0, 0), scratch(4040402, 2**31, 0, 0), scratch(2**31, 5, 0, 0),
+              scratch(1, 5, 2**32 - 1, 0, rn.write_varint(1) + rn.write_varint(2) + rn.write_varint(3)), scratch(1, 5, 2**32, 0),
+              scratch(1, 5, 0, 2**32 - 1), scratch(1, 5, 0, 2**32), scratch(1, 5, 8, 0, rn.write_varint(2**31 - 1) + rn.write_varint(2**32 - 1)),
+              scratch(1, 5, 8, 0, rn.write_varint(2**31) + rn.write_varint(0)), scratch(1, 5, 16, 0, rn.write_varint(0) + rn.write_varint(2**32))]
+    for bad in [good[:-1], good[:10], b"", big_height, rn.write_varint(4040402) + b"\xff" * 12] + limits:
+        got = rn.diskindex_parse(bad)
+        out["disk_index_bad"].append({"raw": bad.hex(), "throws": got is None, "consumed": None if got is None else got[3],
+                                      "height": None if got is None else got[0]["height"]})
+    write("node_glue.json", out)
+
+
 def gen_dag_digest(ref, epoch):
     m = ref.dataset_items(epoch) // 2
     h = hashlib.sha256()
@@ -193,7 +303,7 @@ if __name__ == "__main__":
             gen_dag_digest(ref, e)
     else:
         steps = {"kats": gen_kats, "epochs": gen_epochs, "dag_items": gen_dag_items, "epoch448": gen_epoch448,
-                 "config1": gen_config1}
+                 "config1": gen_config1, "node": gen_node}
         for k, fn in steps.items():
             if not a.only or k in a.only.split(","):
                 fn(ref)

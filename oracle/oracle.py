@@ -403,3 +403,151 @@ class Ref:
         f, m = _buf(32), _buf(32)
         self.L.nxref_ethash_hash(self.ctx(epoch), _in(header), nonce, f, m)
         return bytes(f), bytes(m)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Node-side glue, reference-compiled (oracle/ref_node_shim.cpp -> oracle/_ref/libnxref_node.so; `make -C oracle ref_node`).
+REF_NODE_SO = os.path.join(HERE, "_ref", "libnxref_node.so")
+
+
+class _NodeFields(C.Structure):
+    _fields_ = [("version", C.c_int32), ("prev_block", C.c_uint8 * 32), ("merkle_root", C.c_uint8 * 32),
+                ("time", C.c_uint32), ("bits", C.c_uint32), ("nonce", C.c_uint32), ("height", C.c_uint32),
+                ("nonce64", C.c_uint64), ("mix_hash", C.c_uint8 * 32)]
+
+
+class _NodeDiskIndex(C.Structure):
+    _fields_ = [("height", C.c_int32), ("status", C.c_uint32), ("tx_count", C.c_uint32), ("file", C.c_int32),
+                ("data_pos", C.c_uint32), ("undo_pos", C.c_uint32), ("header", _NodeFields)]
+
+
+class RefNode:
+    """The reference's own CBlockHeader / KAWPOWHash / arith_uint256 / CDiskBlockIndex code.  uint256 arguments and
+    results are raw storage bytes (what `begin()` points at), i.e. the byte-reverse of GetHex()."""
+    kind = "reference"
+
+    def __init__(self, activation_time: int = 1651444217):  # chainparams.cpp:264 (main)
+        if not os.path.exists(REF_NODE_SO):
+            if not os.path.isdir("/root/reference/src"):
+                raise FileNotFoundError(REF_NODE_SO)
+            subprocess.check_call(["make", "-s", "-C", HERE, "ref_node"])
+        L = self.L = C.CDLL(REF_NODE_SO)
+        F, D = C.POINTER(_NodeFields), C.POINTER(_NodeDiskIndex)
+        L.nxrefnode_set_activation_time.argtypes = [C.c_uint32]
+        L.nxrefnode_header_hash.argtypes = [F, u8p, u8p]
+        L.nxrefnode_kawpow_hash.argtypes = [F, u8p, u8p]
+        L.nxrefnode_block_hash.argtypes = [F, u8p]
+        L.nxrefnode_block_hash_full.argtypes = [F, u8p, u8p]
+        L.nxrefnode_serialize_header.argtypes = [F, u8p, C.c_int]
+        L.nxrefnode_parse_header.argtypes = [u8p, C.c_int, F]
+        L.nxrefnode_serialize_kawpow_input.argtypes = [F, u8p]
+        L.nxrefnode_set_compact.argtypes = [C.c_uint32, u8p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.nxrefnode_get_compact.argtypes = [u8p]
+        L.nxrefnode_get_compact.restype = C.c_uint32
+        L.nxrefnode_check_pow.argtypes = [u8p, C.c_uint32, u8p]
+        L.nxrefnode_get_hex.argtypes = [u8p, C.c_char_p]
+        L.nxrefnode_set_hex.argtypes = [C.c_char_p, u8p]
+        L.nxrefnode_write_varint.argtypes = [C.c_uint64, u8p]
+        L.nxrefnode_read_varint.argtypes = [u8p, C.c_int, C.POINTER(C.c_uint64)]
+        L.nxrefnode_diskindex_serialize.argtypes = [D, u8p, C.c_int]
+        L.nxrefnode_diskindex_parse.argtypes = [u8p, C.c_int, D, C.POINTER(C.c_int32), u8p]
+        self.activation_time = activation_time
+        L.nxrefnode_set_activation_time(activation_time)
+
+    def set_activation_time(self, t: int):
+        self.activation_time = t
+        self.L.nxrefnode_set_activation_time(t)
+
+    @staticmethod
+    def fields(version, prev, merkle, time, bits, height, nonce64=0, mix=bytes(32), nonce=0) -> _NodeFields:
+        return _NodeFields(version, (C.c_uint8 * 32)(*prev), (C.c_uint8 * 32)(*merkle), time, bits, nonce, height, nonce64,
+                           (C.c_uint8 * 32)(*mix))
+
+    def header_hash(self, f):
+        """(GetKAWPOWHeaderHash() raw bytes, the hash256 hash.cpp:269-270 hands to progpow::hash)"""
+        a, b = _buf(32), _buf(32)
+        self.L.nxrefnode_header_hash(C.byref(f), a, b)
+        return bytes(a), bytes(b)
+
+    def kawpow_hash(self, f):
+        """KAWPOWHash (hash.cpp:258-279) -> (final, mix) as uint256 raw bytes"""
+        a, b = _buf(32), _buf(32)
+        self.L.nxrefnode_kawpow_hash(C.byref(f), a, b)
+        return bytes(a), bytes(b)
+
+    def block_hash(self, f) -> bytes:
+        a = _buf(32)
+        self.L.nxrefnode_block_hash(C.byref(f), a)
+        return bytes(a)
+
+    def block_hash_full(self, f):
+        a, b = _buf(32), _buf(32)
+        self.L.nxrefnode_block_hash_full(C.byref(f), a, b)
+        return bytes(a), bytes(b)
+
+    def serialize_header(self, f) -> bytes:
+        o = _buf(256)
+        n = self.L.nxrefnode_serialize_header(C.byref(f), o, 256)
+        return bytes(o[:n])
+
+    def parse_header(self, raw: bytes):
+        f = _NodeFields()
+        used = self.L.nxrefnode_parse_header(_in(raw), len(raw), C.byref(f))
+        return (f, used) if used >= 0 else (None, -1)
+
+    def kawpow_input(self, f) -> bytes:
+        o = _buf(80)
+        assert self.L.nxrefnode_serialize_kawpow_input(C.byref(f), o) == 80
+        return bytes(o)
+
+    def set_compact(self, bits: int):
+        """arith_uint256::SetCompact -> (value as 32 big-endian bytes, negative, overflow)"""
+        o, neg, ovf = _buf(32), C.c_int(), C.c_int()
+        self.L.nxrefnode_set_compact(bits, o, C.byref(neg), C.byref(ovf))
+        return bytes(o), bool(neg.value), bool(ovf.value)
+
+    def get_compact(self, be: bytes) -> int:
+        return self.L.nxrefnode_get_compact(_in(be))
+
+    def check_pow(self, hash_raw: bytes, bits: int, limit_raw: bytes) -> bool:
+        return bool(self.L.nxrefnode_check_pow(_in(hash_raw), bits, _in(limit_raw)))
+
+    def get_hex(self, raw: bytes) -> str:
+        o = C.create_string_buffer(65)
+        self.L.nxrefnode_get_hex(_in(raw), o)
+        return o.value.decode()
+
+    def set_hex(self, text: str) -> bytes:
+        o = _buf(32)
+        self.L.nxrefnode_set_hex(text.encode(), o)
+        return bytes(o)
+
+    def write_varint(self, n: int) -> bytes:
+        o = _buf(10)
+        return bytes(o[:self.L.nxrefnode_write_varint(n, o)])
+
+    def read_varint(self, data: bytes):
+        v = C.c_uint64()
+        used = self.L.nxrefnode_read_varint(_in(data) if data else _buf(1), len(data), C.byref(v))
+        return (v.value, used) if used >= 0 else (None, -1)
+
+    def diskindex_serialize(self, height, status, tx_count, file, data_pos, undo_pos, f) -> bytes:
+        d = _NodeDiskIndex(height, status, tx_count, file, data_pos, undo_pos, f)
+        o = _buf(256)
+        n = self.L.nxrefnode_diskindex_serialize(C.byref(d), o, 256)
+        return bytes(o[:n])
+
+    def diskindex_parse(self, raw: bytes):
+        """-> (dict of fields, client_version, GetBlockHash() raw bytes or None, bytes consumed) or None if it throws"""
+        d, cv, h = _NodeDiskIndex(), C.c_int32(), _buf(32)
+        used = self.L.nxrefnode_diskindex_parse(_in(raw) if raw else _buf(1), len(raw), C.byref(d), C.byref(cv), h)
+        if used < 0:
+            return None
+        f = d.header
+        rec = {"height": d.height, "status": d.status, "tx_count": d.tx_count, "file": d.file, "data_pos": d.data_pos,
+               "undo_pos": d.undo_pos, "version": f.version, "prev_block": bytes(f.prev_block), "merkle_root": bytes(f.merkle_root),
+               "time": f.time, "bits": f.bits, "nonce": f.nonce, "nonce64": f.nonce64, "mix_hash": bytes(f.mix_hash)}
+        return rec, cv.value, (bytes(h) if f.time >= self.activation_time else None), used
+
+    def client_version(self) -> int:
+        return self.L.nxrefnode_client_version()
