@@ -180,3 +180,16 @@ def test_kawpow_hash_of_whole_headers_vs_reference_KAWPOWHash(nx, ctx_of):
         assert r.final_hash[::-1].hex() == d["final_uint256"] and r.mix_hash[::-1].hex() == d["mix_uint256"]
         h.mix_hash = r.mix_hash[::-1]
         assert h.block_hash().hex() == d["final_uint256"]  # GetHash() of a block carrying the right mix == GetHashFull()
+
+
+def test_pre_activation_wire_header_layout():
+    """block.h:61-74: before nKAWPOWActivationTime a header is the classic 80 bytes ending in the 32-bit nNonce (X16R era -
+    hashing those is out of scope, but the block-index reader must know the layout to skip over such records)."""
+    for d in G["pre_activation_headers"]:
+        raw = struct.pack("<i32s32sIII", d["version"], bytes.fromhex(d["prev_block"]), bytes.fromhex(d["merkle_root"]), d["time"],
+                          d["bits"], d["nonce"])
+        assert raw.hex() == d["wire"] and len(raw) == 80 and d["time"] < ACT
+        rec = node.DiskBlockIndex(G["client_version"], 1, 0, 0, version=d["version"], prev_block=raw[4:36], merkle_root=raw[36:68],
+                                  time=d["time"], bits=d["bits"], nonce=d["nonce"])
+        blob = rec.serialize(ACT)
+        assert blob.endswith(raw) and node.DiskBlockIndex.parse(blob, ACT)[0] == rec and rec.check(ACT)[0] == -1
