@@ -47,8 +47,8 @@ $(LIB): $(OBJS)
 oracle:
 	$(MAKE) -C oracle oracle
 
-ref:
-	$(MAKE) -C oracle ref
+ref: lib
+	$(MAKE) -C oracle ref ref_tests ref_node_dropin
 
 clean:
 	rm -rf build $(LIB) $(SRC)/kawpow_kernel_src.inc

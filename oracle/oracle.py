@@ -408,6 +408,7 @@ class Ref:
 # ---------------------------------------------------------------------------------------------------------------------
 # Node-side glue, reference-compiled (oracle/ref_node_shim.cpp -> oracle/_ref/libnxref_node.so; `make -C oracle ref_node`).
 REF_NODE_SO = os.path.join(HERE, "_ref", "libnxref_node.so")
+REF_NODE_DROPIN_SO = os.path.join(HERE, "_ref", "libnxref_node_dropin.so")
 
 
 class _NodeFields(C.Structure):
@@ -426,12 +427,16 @@ class RefNode:
     results are raw storage bytes (what `begin()` points at), i.e. the byte-reverse of GetHex()."""
     kind = "reference"
 
-    def __init__(self, activation_time: int = 1651444217):  # chainparams.cpp:264 (main)
-        if not os.path.exists(REF_NODE_SO):
+    def __init__(self, activation_time: int = 1651444217, dropin: bool = False):  # chainparams.cpp:264 (main)
+        """dropin=True loads libnxref_node_dropin.so instead: the SAME reference block.cpp / hash.cpp, compiled against this
+        repository's headers and linked with libnxkawpow.so - the reference's glue running over the product (needs a GPU
+        for the full hash, none for the mix-only one)."""
+        so, target = (REF_NODE_DROPIN_SO, "ref_node_dropin") if dropin else (REF_NODE_SO, "ref_node")
+        if not os.path.exists(so):
             if not os.path.isdir("/root/reference/src"):
-                raise FileNotFoundError(REF_NODE_SO)
-            subprocess.check_call(["make", "-s", "-C", HERE, "ref_node"])
-        L = self.L = C.CDLL(REF_NODE_SO)
+                raise FileNotFoundError(so)
+            subprocess.check_call(["make", "-s", "-C", HERE, target])
+        L = self.L = C.CDLL(so)
         F, D = C.POINTER(_NodeFields), C.POINTER(_NodeDiskIndex)
         L.nxrefnode_set_activation_time.argtypes = [C.c_uint32]
         L.nxrefnode_header_hash.argtypes = [F, u8p, u8p]

@@ -75,3 +75,26 @@ def test_c_example_mines_and_verifies(tmp_path, gpu):
     """examples/mine_and_verify.c: the node-side flow in plain C99 over the C ABI."""
     out = subprocess.run([str(_build_c_example(tmp_path))], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and out.stdout.strip().endswith("OK"), out.stdout[-1000:] + out.stderr[-1000:]
+
+
+REF_TESTS = os.path.join(ROOT, "oracle", "_ref", "kawpow_tests_reference")
+
+
+def test_reference_test_file_builds_against_dropin_headers():
+    """The reference's own src/test/kawpow_tests.cpp, unmodified, compiles against include/crypto/ethash/... and links with
+    libnxkawpow.so (oracle/Makefile `ref_tests`).  Only where /root/reference exists; the binary then travels to the GPU box."""
+    if not os.path.isdir("/root/reference/src/test"):
+        pytest.skip("reference tree not present here")
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "ref_tests"])
+    assert os.path.exists(REF_TESTS)
+
+
+@pytest.mark.gpu
+def test_reference_test_file_passes_on_the_gpu(gpu):
+    """kawpow_l1_cache, kawpow_hash_empty (1000 heights), kawpow_hash_30000, kawpow_hash_and_verify (13 vectors + negatives),
+    kawpow_search - the reference's test cases, the reference's source file, this repository's implementation."""
+    if not os.path.exists(REF_TESTS):
+        pytest.skip("oracle/_ref/kawpow_tests_reference was not built (needs /root/reference at build time)")
+    out = subprocess.run([REF_TESTS], capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "*** 5 test cases" in out.stdout and " 0 failures" in out.stdout, out.stdout[-500:]

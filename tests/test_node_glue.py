@@ -193,3 +193,36 @@ def test_pre_activation_wire_header_layout():
                                   time=d["time"], bits=d["bits"], nonce=d["nonce"])
         blob = rec.serialize(ACT)
         assert blob.endswith(raw) and node.DiskBlockIndex.parse(blob, ACT)[0] == rec and rec.check(ACT)[0] == -1
+
+
+def _dropin():
+    from oracle.oracle import REF_NODE_DROPIN_SO, RefNode
+    if not os.path.exists(REF_NODE_DROPIN_SO) and not os.path.isdir("/root/reference/src"):
+        pytest.skip("oracle/_ref/libnxref_node_dropin.so not built here")
+    return RefNode(ACT, dropin=True)
+
+
+def test_reference_glue_over_the_product_library_host_part():
+    """The reference's own hash.cpp / block.cpp, unmodified, compiled against include/ and linked with libnxkawpow.so
+    (oracle/Makefile `ref_node_dropin`): GetKAWPOWHeaderHash and GetHash() (= KAWPOWHash_OnlyMix -> the product's
+    progpow::hash_no_verify) give what the pure reference build gave.  No GPU needed for these two."""
+    rn = _dropin()
+    for d in G["headers"]:
+        f = rn.fields(d["version"], bytes.fromhex(d["prev_block"]), bytes.fromhex(d["merkle_root"]), d["time"], d["bits"], d["height"],
+                      d["nonce64"], bytes.fromhex(d["mix_hash"]))
+        assert rn.header_hash(f)[1].hex() == d["header_hash_progpow"]
+        assert rn.block_hash(f).hex() == d["block_hash"]
+
+
+@pytest.mark.gpu
+def test_reference_KAWPOWHash_glue_over_the_gpu(gpu):
+    """hash.cpp:258-279 as the node would run it after swapping the library: the reference's KAWPOWHash (static context,
+    GetHex/to_hash256 round trips, uint256S of the result) calling this repository's ethash_create_epoch_context and
+    progpow::hash on the GPU - and returning exactly what the all-reference build returned."""
+    rn = _dropin()
+    for d in G["kawpow_hash"]:
+        f = rn.fields(d["version"], bytes.fromhex(d["prev_block"]), bytes.fromhex(d["merkle_root"]), d["time"], d["bits"], d["height"],
+                      d["nonce64"], bytes.fromhex(d["mix_hash"]))
+        fin, mix = rn.kawpow_hash(f)
+        assert (fin.hex(), mix.hex()) == (d["final_uint256"], d["mix_uint256"])
+        assert rn.block_hash_full(f) == (fin, mix)          # CBlockHeader::GetHashFull (block.cpp:58-76)
