@@ -136,6 +136,57 @@ int main()
         printf("pow_check=%d\n", nx_check_proof_of_work(fin, 0x207fffffu, nullptr));
         printf("ethash_final=%d\n", nx_ethash_verify_final_hash(hh, h.mix_hash, 5, fin));
     }
+    // block-index records: parse exact-size heap copies of random bytes, of a valid record cut at every length, and of
+    // that record with every single bit of its first 16 bytes flipped - any read past the buffer trips ASan
+    {
+        nx_disk_block_index rec;
+        std::memset(&rec, 0, sizeof rec);
+        rec.client_version = 4040402;
+        rec.height = 3360000;
+        rec.status = NX_BLOCK_HAVE_DATA | NX_BLOCK_HAVE_UNDO | 5;
+        rec.tx_count = 77;
+        rec.file = 12;
+        rec.data_pos = 0xfedcba98u;
+        rec.undo_pos = 123456;
+        rec.version = 0x30000000;
+        rec.time = 1700000000u;
+        rec.bits = 0x1b0404cbu;
+        rec.nonce64 = 0x0123456789abcdefull;
+        for (int i = 0; i < 32; ++i) rec.prev_block[i] = rec.merkle_root[i] = rec.mix_hash[i] = (uint8_t)(i + 1);
+        uint8_t full[256];
+        const size_t n = nx_disk_block_index_serialize(&rec, 1651444217u, full, sizeof full);
+        printf("disk_record=%zu:%s\n", n, hex(full, n).c_str());
+        unsigned long long accepted = 0, state = 88172645463325252ull;
+        auto rnd = [&state]() {
+            state ^= state << 13;
+            state ^= state >> 7;
+            state ^= state << 17;
+            return state;
+        };
+        nx_disk_block_index out;
+        for (size_t cut = 0; cut <= n; ++cut) {
+            std::vector<uint8_t> b(full, full + cut);
+            accepted += nx_disk_block_index_parse(b.data(), b.size(), 1651444217u, &out) != 0;
+            uint8_t small[10];
+            if (nx_disk_block_index_serialize(&rec, 1651444217u, small, cut < sizeof small ? cut : sizeof small) != 0) return 3;
+        }
+        for (int bit = 0; bit < 128; ++bit) {
+            std::vector<uint8_t> b(full, full + n);
+            b[(size_t)bit / 8] ^= (uint8_t)(1u << (bit % 8));
+            accepted += nx_disk_block_index_parse(b.data(), b.size(), 1651444217u, &out) != 0;
+        }
+        for (int i = 0; i < 20000; ++i) {
+            std::vector<uint8_t> b(rnd() % 141);
+            for (auto& x : b) x = (uint8_t)rnd();
+            if (!b.empty() && (i & 1)) b[0] = (uint8_t)(b[0] & 0x7f);  // half of them start with a one-byte version
+            accepted += nx_disk_block_index_parse(b.data(), b.size(), (uint32_t)rnd(), &out) != 0;
+            uint64_t v;
+            accepted += nx_varint_read(b.data(), b.size(), &v) != 0;
+        }
+        printf("disk_fuzz_accepted=%llu\n", accepted);
+        uint8_t id[32];
+        printf("disk_check=%d\n", nx_disk_block_index_check(&rec, 1651444217u, nullptr, id));
+    }
     puts("done=1");
     return 0;
 }

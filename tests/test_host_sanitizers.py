@@ -77,6 +77,10 @@ def test_values_match_library_and_oracle(san, oracle):
         assert int(got_ok) == int(ok)
         if ok:
             assert got_t == target.hex()
+    n, rec_hex = kv["disk_record"].split(":")
+    rec, used = __import__("nodexa_chain_core_b200.node", fromlist=["x"]).DiskBlockIndex.parse(bytes.fromhex(rec_hex))
+    assert used == int(n) and (rec.height, rec.file, rec.data_pos, rec.nonce64) == (3360000, 12, 0xfedcba98, 0x0123456789abcdef)
+    assert int(kv["disk_fuzz_accepted"]) > 0 and kv["disk_check"] in ("0", "1")
     hh = oracle.kawpow_header_hash(0x30000000, bytes(range(32)), bytes(255 - i for i in range(32)), 1651444217, 0x1b0404cb, 3360000)
     assert kv["header_hash"] == hh.hex() and kv["roundtrip"] == "1"
     mix = bytes((i * 3) & 0xff for i in range(32))
