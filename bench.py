@@ -136,6 +136,40 @@ def cpu_reference_rate_full_dag(ctx, target_s: float, threads: int):
         ref.full_ctx_destroy(full)
 
 
+def cpu_epoch_build_baseline(ctx, epoch: int, threads: int):
+    """CPU baseline for the epoch build, --cpu-baseline-extras only: the reference's light-cache
+    build on one thread (it is a serial chain) and its calculate_dataset_item_2048 on all host cores, extrapolated to the
+    whole DAG; the sampled items are compared with the GPU-built DAG."""
+    from oracle.oracle import Oracle, Ref
+    impl = Ref() if Ref.available() else Oracle()
+    t0 = time.perf_counter()
+    impl.ctx(epoch)
+    light_s = time.perf_counter() - t0
+    cnt = 1 << 14
+    t0 = time.perf_counter()
+    items = impl.dataset_items_2048(epoch, 12345, cnt, threads)
+    dt = time.perf_counter() - t0
+    assert items == ctx.read_items(12345, cnt), "CPU DAG items disagree with the GPU"
+    return {"kind": impl.kind, "cores": threads, "light_cache_plus_l1_s_single_thread": light_s,
+            "dag_items_256B_per_s_all_cores": cnt / dt, "full_dag_extrapolated_s_all_cores": ctx.dag_num_items / (cnt / dt),
+            "sample": f"{cnt} items of 256 B compared with the GPU DAG"}
+
+
+def cpu_equihash_baseline(nonces: int = 2):
+    """--cpu-baseline-extras only: the single-threaded self-consistency oracle of the GATED Equihash engine at (200,9), same
+    headers and tag as tools/bench_equihash.py.  Not a reference number: the reference contains no Equihash."""
+    import hashlib
+
+    from oracle.oracle import Oracle
+    orc = Oracle()
+    base = hashlib.sha512(b"nodexa-equihash-bench").digest() * 3
+    t0 = time.perf_counter()
+    sols = sum(len(orc.equihash_solve(200, 9, b"NodexaPW", base[:108] + i.to_bytes(32, "little"))) for i in range(nonces))
+    dt = time.perf_counter() - t0
+    return {"kind": "port (self-consistency oracle, 1 thread)", "n": 200, "k": 9, "nonces": nonces, "solutions": sols,
+            "sol_per_s": sols / dt, "s_per_nonce": dt / nonces}
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -177,6 +211,8 @@ def main():
     ap.add_argument("--dag-exchange", default="fused", choices=["fused", "nccl"],
                     help="N>1: how the DAG slices reach every GPU - peer stores inside the generating kernel, or NCCL")
     ap.add_argument("--no-full-dag-baseline", action="store_true")
+    ap.add_argument("--cpu-baseline-extras", action="store_true",
+                    help="also time the reference's epoch build on the host cores and the gated Equihash engine's CPU oracle")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
 
@@ -356,6 +392,13 @@ def main():
                         line["cpu_baseline_full_dag"] = full
                 except Exception as e:  # noqa: BLE001 - a baseline extra must never sink the bench line
                     line["cpu_baseline_full_dag"] = {"error": repr(e)[:200]}
+            if args.cpu_baseline_extras:
+                for key, fn in (("cpu_baseline_epoch_build", lambda: cpu_epoch_build_baseline(ctx, epoch, cores)),
+                                ("cpu_baseline_equihash_gated", cpu_equihash_baseline)):
+                    try:
+                        line[key] = fn()
+                    except Exception as e:  # noqa: BLE001
+                        line[key] = {"error": repr(e)[:200]}
         print(json.dumps(line), flush=True)
     ctx.close()
     if dist is not None:

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Equihash solve throughput (Sol/s) of the gated engine on one GPU, next to the CPU oracle on a bounded sample.
+"""Equihash solve throughput (Sol/s) of the gated engine on one GPU (its CPU oracle is timed by `bench.py --cpu-baseline-extras`).
 NOT a comparison with the reference: the reference has no Equihash (SURVEY.md §0 Fact 1)."""
 import argparse
 import hashlib
@@ -21,11 +21,8 @@ def header(nonce: int) -> bytes:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--nonces", type=int, default=64)
-    ap.add_argument("--cpu-nonces", type=int, default=2)
     a = ap.parse_args()
     import nodexa_chain_core_b200 as nx
-    from oracle.oracle import Oracle
-    orc = Oracle()
     res = {"note": "self-consistency only: the reference contains no Equihash; (n,k) and tag are inputs", "runs": []}
     for n, k in ((200, 9), (144, 5)):
         with nx.equihash.Solver(n, k, TAG) as s:
@@ -43,12 +40,6 @@ def main():
             run = {"n": n, "k": k, "nonces": a.nonces, "solutions": sols, "sol_per_s_device": sols / (kernel_ms * 1e-3),
                    "sol_per_s_e2e": sols / wall, "ms_per_nonce_device": kernel_ms / a.nonces, "ms_per_nonce_e2e": wall / a.nonces * 1e3,
                    "launches_per_nonce": s.last_timing()[1], "rows_dropped": dropped, "candidates": cands}
-            if (n, k) == (200, 9) and a.cpu_nonces:
-                t0 = time.perf_counter()
-                cs = sum(len(orc.equihash_solve(n, k, TAG, header(i))) for i in range(a.cpu_nonces))
-                dt = time.perf_counter() - t0
-                run["cpu_oracle"] = {"kind": "port (self-consistency oracle, 1 thread)", "nonces": a.cpu_nonces, "solutions": cs,
-                                     "sol_per_s": cs / dt, "s_per_nonce": dt / a.cpu_nonces}
             res["runs"].append(run)
     print(json.dumps(res))
 

@@ -79,25 +79,7 @@ def main():
     ethash.hash_batch(ctx, hd, 1 << 32, n7)
     kms, _ = ctx.last_timing()
     res["K7_ethash_hash"] = {"nonces": n7, "kernel_MHs": n7 / kms / 1e3, "dag_GBps": n7 * 8192 / kms / 1e6}
-    # CPU baselines for the epoch build: the reference's own code on the host cores
-    try:
-        from oracle.oracle import Oracle, Ref
-        impl = Ref() if Ref.available() else Oracle()
-        cores = os.cpu_count() or 1
-        t0 = time.perf_counter()
-        impl.ctx(a.epoch)
-        light_s = time.perf_counter() - t0
-        cnt = 1 << 14
-        t0 = time.perf_counter()
-        items = impl.dataset_items_2048(a.epoch, 12345, cnt, cores)
-        dt = time.perf_counter() - t0
-        assert items == ctx.read_items(12345, cnt), "CPU DAG items disagree with the GPU"
-        res["cpu_epoch_build"] = {"kind": impl.kind, "cores": cores, "light_cache_plus_l1_s_single_thread": light_s,
-                                  "dag_items_256B_per_s_all_cores": cnt / dt,
-                                  "full_dag_extrapolated_s_all_cores": ctx.dag_num_items / (cnt / dt),
-                                  "sample": f"{cnt} items of 256 B compared with the GPU DAG"}
-    except Exception as e:  # noqa: BLE001
-        res["cpu_epoch_build"] = {"error": repr(e)[:200]}
+    # the CPU side of the epoch build (reference code on the host cores) is timed by `bench.py --cpu-baseline-extras`
     print(json.dumps(res))
     ctx.close()
 
