@@ -245,3 +245,29 @@ def test_cached_period_is_not_blocked_by_a_compile_in_another_thread(ctx_of):
     th.join()
     assert len(got) == 64 * 64
     assert cached_s < 0.5 * compile_s, (cached_s, compile_s)
+
+
+@pytest.mark.parametrize("epoch", [1, 129, 300])
+def test_other_epochs_live_vs_oracle(nx, oracle, epoch):
+    """Epochs no fixture covers (other DAG sizes, other prime divisors for every `% n` on the path): DAG items, compiled
+    KawPow (K2), interpreted KawPow (K6) and classic Ethash (K7) against the CPU oracle running on this box."""
+    from nodexa_chain_core_b200 import ethash
+    rnd = random.Random(epoch)
+    ctx = nx.EpochContext(epoch, 0)
+    try:
+        assert ctx.dag_num_items == oracle.dataset_items(epoch) // 2 and ctx.light_cache_num_items == oracle.light_items(epoch)
+        m = ctx.dag_num_items
+        for first in (0, m - 8, rnd.randrange(m - 8)):
+            assert ctx.read_items(first, 8) == oracle.dataset_items_2048(epoch, first, 8)
+        height = epoch * 7500 + rnd.randrange(7500)
+        hd = rnd.randbytes(32)
+        start = rnd.getrandbits(64) - 64
+        assert progpow.hash_batch(ctx, height, hd, start, 48) == oracle.kawpow_hash_range(epoch, height, hd, start, 48)
+        recs = [(epoch * 7500 + rnd.randrange(7500), rnd.randbytes(32), rnd.getrandbits(64)) for _ in range(12)]
+        got = progpow.hash_many(ctx, recs)
+        for (bn, h, n), r in zip(recs, got):
+            assert (r.final_hash, r.mix_hash) == oracle.kawpow_hash(epoch, bn, h, n)
+        for n in (0, rnd.getrandbits(64)):
+            assert ethash.hash(ctx, hd, n) == oracle.ethash_hash(epoch, hd, n)
+    finally:
+        ctx.close()
