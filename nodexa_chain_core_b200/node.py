@@ -13,6 +13,9 @@ from .ethash import EpochContext
 HEADER_OK, HEADER_HIGH_HASH, HEADER_INVALID_MIX, HEADER_BAD_BITS, HEADER_WRONG_EPOCH = range(5)
 KAWPOW_LIMIT = bytes.fromhex("00" + "ff" * 31)  # chainparams.cpp:116-117 (main/test)
 MAINNET_KAWPOW_ACTIVATION_TIME = 1651444217      # chainparams.cpp:264
+TESTNET_KAWPOW_ACTIVATION_TIME = 1653247613      # chainparams.cpp:419
+REGTEST_KAWPOW_ACTIVATION_TIME = 3582830167      # chainparams.cpp:569 (year 2083: regtest never reaches KawPow by itself)
+REGTEST_KAWPOW_LIMIT = bytes.fromhex("7f" + "ff" * 31)  # chainparams.cpp:438-439
 
 
 @dataclass
