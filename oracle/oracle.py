@@ -556,3 +556,90 @@ class RefNode:
 
     def client_version(self) -> int:
         return self.L.nxrefnode_client_version()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Plain-Python restatement of the block-index record format (small inputs only), pinned to tests/golden/node_glue.json.
+
+def varint_write(n: int) -> bytes:
+    """WriteVarInt (serialize.h:330-345): MSB base-128, all digits but the last carry bit 7 and have one subtracted."""
+    tmp = []
+    while True:
+        tmp.append((n & 0x7F) | (0x80 if tmp else 0x00))
+        if n <= 0x7F:
+            break
+        n = (n >> 7) - 1
+    return bytes(reversed(tmp))
+
+
+def varint_read(data: bytes, max_value: int = 2**64 - 1):
+    """ReadVarInt<I> (serialize.h:347-366) with I's maximum given: (value, bytes used), or None where it throws."""
+    n = 0
+    for i, c in enumerate(data):
+        if n > (max_value >> 7):
+            return None
+        n = (n << 7) | (c & 0x7F)
+        if c & 0x80:
+            if n == max_value:
+                return None
+            n += 1
+        else:
+            return n, i + 1
+    return None  # the stream ran dry: ser_readdata8 throws
+
+
+def disk_block_index_parse(data: bytes, activation_time: int):
+    """CDiskBlockIndex::SerializationOp, read direction (chain.h:398-431): (dict, bytes used) or None where it throws.
+    Field types: _nVersion/nHeight/nFile int, nStatus uint32_t, nTx/nDataPos/nUndoPos unsigned int (chain.h:185-209)."""
+    import struct
+    I32, U32 = 2**31 - 1, 2**32 - 1
+    p, rec = 0, {"file": 0, "data_pos": 0, "undo_pos": 0, "nonce": 0, "nonce64": 0, "mix_hash": bytes(32)}
+
+    def take(name, mx):
+        nonlocal p
+        got = varint_read(data[p:], mx)
+        if got is None:
+            return False
+        rec[name], used = got
+        p += used
+        return True
+
+    if not (take("client_version", I32) and take("height", I32) and take("status", U32) and take("tx_count", U32)):
+        return None
+    if rec["status"] & (8 | 16) and not take("file", I32):   # BLOCK_HAVE_DATA | BLOCK_HAVE_UNDO (chain.h:156-157)
+        return None
+    if rec["status"] & 8 and not take("data_pos", U32):
+        return None
+    if rec["status"] & 16 and not take("undo_pos", U32):
+        return None
+    if len(data) - p < 76:
+        return None
+    rec["version"], rec["prev_block"], rec["merkle_root"], rec["time"], rec["bits"] = struct.unpack_from("<i32s32sII", data, p)
+    p += 76
+    if rec["time"] < activation_time:
+        if len(data) - p < 4:
+            return None
+        (rec["nonce"],) = struct.unpack_from("<I", data, p)
+        p += 4
+    else:
+        if len(data) - p < 40:
+            return None
+        rec["nonce64"], rec["mix_hash"] = struct.unpack_from("<Q32s", data, p)
+        p += 40
+    return rec, p
+
+
+def disk_block_index_serialize(rec: dict, activation_time: int) -> bytes:
+    """CDiskBlockIndex::SerializationOp, write direction (chain.h:398-431)."""
+    import struct
+    out = varint_write(rec["client_version"]) + varint_write(rec["height"]) + varint_write(rec["status"]) + varint_write(rec["tx_count"])
+    if rec["status"] & (8 | 16):
+        out += varint_write(rec["file"])
+    if rec["status"] & 8:
+        out += varint_write(rec["data_pos"])
+    if rec["status"] & 16:
+        out += varint_write(rec["undo_pos"])
+    out += struct.pack("<i32s32sII", rec["version"], rec["prev_block"], rec["merkle_root"], rec["time"], rec["bits"])
+    if rec["time"] < activation_time:
+        return out + struct.pack("<I", rec["nonce"])
+    return out + struct.pack("<Q32s", rec["nonce64"], rec["mix_hash"])

@@ -226,3 +226,51 @@ def test_reference_KAWPOWHash_glue_over_the_gpu(gpu):
         fin, mix = rn.kawpow_hash(f)
         assert (fin.hex(), mix.hex()) == (d["final_uint256"], d["mix_uint256"])
         assert rn.block_hash_full(f) == (fin, mix)          # CBlockHeader::GetHashFull (block.cpp:58-76)
+
+
+def test_python_restatement_of_the_record_format_and_product_agree():
+    """oracle.oracle.varint_* / disk_block_index_* (plain Python, pinned to the reference-made fixtures here) against the
+    product on random and damaged records - the checker that also exists where oracle/_ref does not."""
+    from oracle import oracle as orc
+    for v in G["varint"]:
+        assert orc.varint_write(int(v["n"])).hex() == v["bytes"] and orc.varint_read(bytes.fromhex(v["bytes"])) == (int(v["n"]), len(v["bytes"]) // 2)
+    for v in G["varint_bad"]:
+        assert (orc.varint_read(bytes.fromhex(v["bytes"])) is None) == v["throws"]
+    for d in G["disk_index"]:
+        raw = bytes.fromhex(d["raw"])
+        rec, used = orc.disk_block_index_parse(raw, ACT)
+        assert used == len(raw) and orc.disk_block_index_serialize(rec, ACT) == raw
+        for k, want in d["record"].items():
+            assert (rec[k].hex() if isinstance(rec[k], bytes) else rec[k]) == want, k
+    for d in G["disk_index_bad"]:
+        got = orc.disk_block_index_parse(bytes.fromhex(d["raw"]), ACT)
+        assert (got is None) == d["throws"] and (got is None or (got[1], got[0]["height"]) == (d["consumed"], d["height"]))
+    rnd = random.Random(99)
+    for _ in range(3000):
+        act = rnd.choice([0, ACT, 2**32 - 1])
+        rec = {"client_version": rnd.getrandbits(rnd.randrange(1, 32)), "height": rnd.getrandbits(rnd.randrange(1, 32)),
+               "status": rnd.getrandbits(rnd.randrange(1, 33)), "tx_count": rnd.getrandbits(rnd.randrange(1, 33)),
+               "file": rnd.getrandbits(20), "data_pos": rnd.getrandbits(32), "undo_pos": rnd.getrandbits(32),
+               "version": rnd.randrange(-2**31, 2**31), "prev_block": rnd.randbytes(32), "merkle_root": rnd.randbytes(32),
+               "time": rnd.getrandbits(32), "bits": rnd.getrandbits(32), "nonce": rnd.getrandbits(32), "nonce64": rnd.getrandbits(64),
+               "mix_hash": rnd.randbytes(32)}
+        raw = orc.disk_block_index_serialize(rec, act)
+        mine = node.DiskBlockIndex(rec["client_version"], rec["height"], rec["status"], rec["tx_count"], rec["file"], rec["data_pos"],
+                                   rec["undo_pos"], rec["version"], rec["prev_block"], rec["merkle_root"], rec["time"], rec["bits"],
+                                   rec["nonce"], rec["nonce64"], rec["mix_hash"])
+        assert mine.serialize(act) == raw
+        damaged = bytearray(raw[:rnd.randrange(len(raw) + 1)] if rnd.random() < 0.5 else raw)
+        if damaged and rnd.random() < 0.7:
+            damaged[rnd.randrange(min(len(damaged), 14))] ^= 1 << rnd.randrange(8)
+        theirs = orc.disk_block_index_parse(bytes(damaged), act)
+        if theirs is None:
+            with pytest.raises(ValueError):
+                node.DiskBlockIndex.parse(bytes(damaged), act)
+        else:
+            got, used = node.DiskBlockIndex.parse(bytes(damaged), act)
+            assert used == theirs[1]
+            t = theirs[0]
+            assert (got.client_version, got.height, got.status, got.tx_count, got.file, got.data_pos, got.undo_pos, got.version,
+                    got.time, got.bits, got.nonce, got.nonce64, got.prev_block, got.merkle_root, got.mix_hash) == \
+                   (t["client_version"], t["height"], t["status"], t["tx_count"], t["file"], t["data_pos"], t["undo_pos"], t["version"],
+                    t["time"], t["bits"], t["nonce"], t["nonce64"], t["prev_block"], t["merkle_root"], t["mix_hash"])
