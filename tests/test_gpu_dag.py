@@ -136,3 +136,30 @@ def test_epoch_that_does_not_fit_the_device_fails_cleanly(nx, gpu, ctx_of):
     assert e.value.code == -4 and "cudaMalloc" in str(e.value)
     ctx = ctx_of(0)
     assert ctx.l1_cache[:20] == golden("kawpow_kats.json")["l1_epoch0_first20"]
+
+
+def test_contexts_give_all_device_memory_back(nx, gpu):
+    """A node changes epoch every 7500 blocks for as long as it runs: creating and destroying contexts (directly, and through
+    the miner's epoch hand-over with its background prebuild) must not leak device memory."""
+    import torch
+    torch.cuda.init()
+    torch.cuda.synchronize()
+
+    def free_bytes():
+        torch.cuda.synchronize()
+        return torch.cuda.mem_get_info(0)[0]
+
+    nx.EpochContext(0, gpu).close()   # first use: CUDA context, module loading, allocator pools settle
+    base = free_bytes()
+    for e in (0, 1, 2, 0, 1, 2):
+        c = nx.EpochContext(e, gpu)
+        assert free_bytes() < base - (1 << 30)          # the 1 GiB+ DAG is really resident
+        c.close()
+    assert abs(free_bytes() - base) <= (8 << 20), (base, free_bytes())
+    with nx.Miner([gpu]) as m:
+        hd = bytes(range(32))
+        for height in (7499, 7500, 15000, 7499):
+            m.prepare_async(height, lookahead_blocks=2)
+            assert m.search(height, hd, b"\xff" * 32, 0, 1).solution_found
+        m.wait_prepared()
+    assert abs(free_bytes() - base) <= (8 << 20), (base, free_bytes())
