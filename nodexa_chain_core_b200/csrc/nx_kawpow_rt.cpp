@@ -7,9 +7,11 @@
 #include "nx_internal.hpp"
 
 #include <dlfcn.h>
+#include <unistd.h>
 #include <nvrtc.h>
 
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
@@ -253,14 +255,24 @@ static int get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
             if (!path.empty()) {
                 std::ifstream f(path, std::ios::binary);
                 if (f) fresh->assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
+                // a file that is not a whole ELF image (foreign, truncated by a crash) is ignored and rewritten
+                if (fresh->size() < 64 || std::memcmp(fresh->data(), "\x7f" "ELF", 4) != 0) fresh->clear();
             }
             if (fresh->empty()) {
                 std::string log;
                 const int rc = compile_cubin(prog_seed, dag_items, *fresh, log);
                 if (rc != NX_OK) return rc;
                 if (!path.empty()) {
-                    std::ofstream f(path, std::ios::binary);
-                    f.write(fresh->data(), (std::streamsize)fresh->size());
+                    // several processes (one per GPU) may compile the same period at the same time: write beside the
+                    // final name and rename, so that no reader ever sees a half-written cubin
+                    const std::string tmp = path + ".tmp." + std::to_string((long)getpid());
+                    bool ok = false;
+                    {
+                        std::ofstream f(tmp, std::ios::binary);
+                        f.write(fresh->data(), (std::streamsize)fresh->size());
+                        ok = f.good();
+                    }
+                    if (!ok || std::rename(tmp.c_str(), path.c_str()) != 0) std::remove(tmp.c_str());
                 }
             }
             while (g_cubins.size() >= 8) g_cubins.erase(g_cubins.begin());  // lowest period first: heights ascend

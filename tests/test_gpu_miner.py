@@ -146,6 +146,13 @@ def test_program_cache_dir_persists_compiled_periods(tmp_path):
         import re
         return float(re.search(r": ([0-9.]+) ms, regs", stderr).group(1))
     assert compile_ms(second.stderr) < compile_ms(first.stderr)  # loading a cubin beats NVRTC
+    # a damaged cache file (a crash mid-write under an older version, a foreign file) is ignored and replaced
+    path = os.path.join(tmp_path, files[0])
+    good = open(path, "rb").read()
+    open(path, "wb").write(good[:1000].replace(b"\x7fELF", b"\x7fELG"))
+    third = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert third.returncode == 0 and third.stdout == first.stdout, third.stderr[-2000:]
+    assert sorted(os.listdir(tmp_path)) == files and len(open(path, "rb").read()) == len(good)
 
 
 def test_chain_across_period_switches_and_an_epoch_boundary(nx, oracle):
