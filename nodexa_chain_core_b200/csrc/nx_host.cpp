@@ -3,6 +3,8 @@
 #include "nx_internal.hpp"
 #include "nx_keccak.cuh"
 
+#include <unistd.h>
+
 #include <cstdarg>
 #include <cstdlib>
 #include <cstring>
@@ -101,7 +103,7 @@ void host_store_light_cache(const uint8_t* cache, int n, int epoch)
 {
     const std::string path = light_path(epoch);
     if (path.empty()) return;
-    const std::string tmp = path + ".tmp";
+    const std::string tmp = path + ".tmp." + std::to_string((long)getpid());  // one process per GPU may build the same epoch
     FILE* f = std::fopen(tmp.c_str(), "wb");
     if (!f) return;
     LightFileHeader h;
