@@ -10,6 +10,9 @@
 #include "kats_generated.hpp"  // struct kat {int block_number; const char *header, *nonce, *mix, *final;}; kats[], l1_expected[], kat30000
 
 #include <array>
+#include <atomic>
+#include <thread>
+#include <vector>
 #include <cstdio>
 #include <cstdlib>
 #include <string>
@@ -130,6 +133,35 @@ static void managed_and_classic()
     }
 }
 
+// hash.cpp:260-266 keeps ONE function-static context and is called from the miner threads, the RPC threads and the
+// validation thread at once - a data race across an epoch change in the reference.  The managed
+// accessors are the thread-safe way (managed.cpp:23-100): every thread may ask for either epoch at any time, the
+// pointer it got stays valid until IT asks again, and the hashes are right throughout.
+static void managed_threads()
+{
+    const auto h = to_hash256(kats[0].header);
+    const auto want0 = progpow::hash(ethash::get_global_epoch_context(0), 0, h, 0);
+    const auto want1 = progpow::hash(ethash::get_global_epoch_context(1), 7500, h, 0);
+    CHECK(!(want0.final_hash == want1.final_hash));
+    std::atomic<int> bad{0};
+    std::vector<std::thread> th;
+    for (int t = 0; t < 4; ++t)
+        th.emplace_back([&, t] {
+            for (int i = 0; i < 3; ++i) {
+                const int epoch = (t + i) & 1;
+                const auto& ctx = ethash::get_global_epoch_context(epoch);
+                if (ctx.epoch_number != epoch) ++bad;
+                for (int k = 0; k < 4; ++k) {  // keeps using its pointer while the other threads switch the shared one
+                    const auto r = progpow::hash(ctx, epoch ? 7500 : 0, h, 0);
+                    const auto& want = epoch ? want1 : want0;
+                    if (!(r.final_hash == want.final_hash) || !(r.mix_hash == want.mix_hash)) ++bad;
+                }
+            }
+        });
+    for (auto& x : th) x.join();
+    CHECK(bad.load() == 0);
+}
+
 int main()
 {
     kawpow_l1_cache();
@@ -138,6 +170,7 @@ int main()
     kawpow_hash_and_verify();
     kawpow_search();
     managed_and_classic();
+    managed_threads();
     if (failures) {
         std::printf("%d CHECK(s) FAILED\n", failures);
         return 1;

@@ -29,7 +29,7 @@ def _build(tmp_path):
     _gen_header(tmp_path / "kats_generated.hpp")
     exe = tmp_path / "dropin_test"
     libdir = os.path.join(ROOT, "nodexa_chain_core_b200")
-    subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-Wextra", "-I", os.path.join(ROOT, "include"), "-I", str(tmp_path),
+    subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-Wextra", "-pthread", "-I", os.path.join(ROOT, "include"), "-I", str(tmp_path),
                            os.path.join(ROOT, "tests", "cpp", "kawpow_dropin_test.cpp"), "-o", str(exe),
                            "-L", libdir, "-lnxkawpow", f"-Wl,-rpath,{libdir}"])
     return exe
