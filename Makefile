@@ -48,7 +48,7 @@ oracle:
 	$(MAKE) -C oracle oracle
 
 ref: lib
-	$(MAKE) -C oracle ref ref_tests ref_node_dropin
+	$(MAKE) -C oracle ref ref_tests ref_node_dropin ref_node_explicit
 
 clean:
 	rm -rf build $(LIB) $(SRC)/kawpow_kernel_src.inc

@@ -409,6 +409,7 @@ class Ref:
 # Node-side glue, reference-compiled (oracle/ref_node_shim.cpp -> oracle/_ref/libnxref_node.so; `make -C oracle ref_node`).
 REF_NODE_SO = os.path.join(HERE, "_ref", "libnxref_node.so")
 REF_NODE_DROPIN_SO = os.path.join(HERE, "_ref", "libnxref_node_dropin.so")
+REF_NODE_EXPLICIT_SO = os.path.join(HERE, "_ref", "libnxref_node_explicit.so")
 
 
 class _NodeFields(C.Structure):
@@ -427,11 +428,13 @@ class RefNode:
     results are raw storage bytes (what `begin()` points at), i.e. the byte-reverse of GetHex()."""
     kind = "reference"
 
-    def __init__(self, activation_time: int = 1651444217, dropin: bool = False):  # chainparams.cpp:264 (main)
+    def __init__(self, activation_time: int = 1651444217, dropin: bool = False, explicit: bool = False):  # chainparams.cpp:264
         """dropin=True loads libnxref_node_dropin.so instead: the SAME reference block.cpp / hash.cpp, compiled against this
         repository's headers and linked with libnxkawpow.so - the reference's glue running over the product (needs a GPU
         for the full hash, none for the mix-only one)."""
         so, target = (REF_NODE_DROPIN_SO, "ref_node_dropin") if dropin else (REF_NODE_SO, "ref_node")
+        if explicit:  # KAWPOWHash / _OnlyMix from examples/node_patch/hash_kawpow_nx.cpp (INTEGRATION.md section 1)
+            so, target = REF_NODE_EXPLICIT_SO, "ref_node_explicit"
         if not os.path.exists(so):
             if not os.path.isdir("/root/reference/src"):
                 raise FileNotFoundError(so)

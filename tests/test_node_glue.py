@@ -195,18 +195,22 @@ def test_pre_activation_wire_header_layout():
         assert blob.endswith(raw) and node.DiskBlockIndex.parse(blob, ACT)[0] == rec and rec.check(ACT)[0] == -1
 
 
-def _dropin():
-    from oracle.oracle import REF_NODE_DROPIN_SO, RefNode
-    if not os.path.exists(REF_NODE_DROPIN_SO) and not os.path.isdir("/root/reference/src"):
-        pytest.skip("oracle/_ref/libnxref_node_dropin.so not built here")
-    return RefNode(ACT, dropin=True)
+def _dropin(explicit=False):
+    from oracle.oracle import REF_NODE_DROPIN_SO, REF_NODE_EXPLICIT_SO, RefNode
+    so = REF_NODE_EXPLICIT_SO if explicit else REF_NODE_DROPIN_SO
+    if not os.path.exists(so) and not os.path.isdir("/root/reference/src"):
+        pytest.skip(f"{os.path.basename(so)} not built here")
+    return RefNode(ACT, dropin=not explicit, explicit=explicit)
 
 
-def test_reference_glue_over_the_product_library_host_part():
+@pytest.mark.parametrize("explicit", [False, True])
+def test_reference_glue_over_the_product_library_host_part(explicit):
     """The reference's own hash.cpp / block.cpp, unmodified, compiled against include/ and linked with libnxkawpow.so
     (oracle/Makefile `ref_node_dropin`): GetKAWPOWHeaderHash and GetHash() (= KAWPOWHash_OnlyMix -> the product's
-    progpow::hash_no_verify) give what the pure reference build gave.  No GPU needed for these two."""
-    rn = _dropin()
+    progpow::hash_no_verify) give what the pure reference build gave.  No GPU needed for these two.
+    explicit=True: the same with hash.cpp replaced by examples/node_patch/hash_kawpow_nx.cpp, the binding INTEGRATION.md
+    section 1 proposes (`ref_node_explicit`)."""
+    rn = _dropin(explicit)
     for d in G["headers"]:
         f = rn.fields(d["version"], bytes.fromhex(d["prev_block"]), bytes.fromhex(d["merkle_root"]), d["time"], d["bits"], d["height"],
                       d["nonce64"], bytes.fromhex(d["mix_hash"]))
@@ -215,11 +219,13 @@ def test_reference_glue_over_the_product_library_host_part():
 
 
 @pytest.mark.gpu
-def test_reference_KAWPOWHash_glue_over_the_gpu(gpu):
+@pytest.mark.parametrize("explicit", [False, True])
+def test_reference_KAWPOWHash_glue_over_the_gpu(gpu, explicit):
     """hash.cpp:258-279 as the node would run it after swapping the library: the reference's KAWPOWHash (static context,
     GetHex/to_hash256 round trips, uint256S of the result) calling this repository's ethash_create_epoch_context and
-    progpow::hash on the GPU - and returning exactly what the all-reference build returned."""
-    rn = _dropin()
+    progpow::hash on the GPU - and returning exactly what the all-reference build returned.  explicit=True: KAWPOWHash
+    from examples/node_patch/hash_kawpow_nx.cpp (nx_* calls, mutex-guarded context) under the reference's block.cpp."""
+    rn = _dropin(explicit)
     for d in G["kawpow_hash"]:
         f = rn.fields(d["version"], bytes.fromhex(d["prev_block"]), bytes.fromhex(d["merkle_root"]), d["time"], d["bits"], d["height"],
                       d["nonce64"], bytes.fromhex(d["mix_hash"]))
