@@ -164,12 +164,13 @@ typedef struct nx_search_result
 int nx_kawpow_prepare(const nx_epoch* ctx, int block_number);
 
 /* One nonce.  Replaces progpow::hash(ctx, block_number, header_hash, nonce)
- * (crypto/ethash/lib/ethash/progpow.cpp:298-355 and :357-429). */
+ * (crypto/ethash/lib/ethash/progpow.cpp:298-355 and :357-429).  Runs on the interpreted kernel (K6): no NVRTC
+ * compilation is ever waited for, 0.3 ms per call; many nonces of one header belong in nx_kawpow_hash_batch / _search. */
 int nx_kawpow_hash(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32], uint64_t nonce,
                    nx_result* out);
 
 /* `count` consecutive nonces; out = count x {final_hash[32], mix_hash[32]} in HOST memory
- * (kernel K2; the copy back is part of the call). */
+ * (the period's compiled kernel in batch mode; the copy back is part of the call). */
 int nx_kawpow_hash_batch(const nx_epoch* ctx, int block_number, const uint8_t header_hash[32],
                          uint64_t start_nonce, uint64_t count, uint8_t* out_host);
 /* Same, results left in DEVICE memory (count*64 bytes); returns after the kernel completed. */
