@@ -50,6 +50,9 @@ typedef unsigned long long u64;
 #ifndef NX_ROT_IMAD
 #define NX_ROT_IMAD 0
 #endif
+#ifndef NX_DAG_HINT
+#define NX_DAG_HINT 0  // cache hints on the DAG load (see nx_ld_dag)
+#endif
 #ifndef NX_ILV
 #define NX_ILV 1  // nonces a half-warp works on at the same time (1 or 2)
 #endif
@@ -263,9 +266,21 @@ NX_DEV u32 nx_l1_load(u32 x, u32 lane_base, u32 mul_lo, u32 mul_hi)
 NX_DEV uint4 nx_ld_dag(const uint4* p)
 {
     uint4 v;
+#if NX_DAG_HINT == 1  // ask L2 to bring in the whole 256-byte item on the first sector that misses
+    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+#elif NX_DAG_HINT == 2  // plain cached load
+    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+#elif NX_DAG_HINT == 3  // evict-first in L1, 128-byte L2 granularity
+    asm volatile("ld.global.nc.L1::evict_first.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+#else
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                  : "l"(p));
+#endif
     return v;
 }
 

@@ -76,12 +76,12 @@ const char* cu_err(CUresult_ r)
 // NX_KAWPOW_TUNE overrides them, e.g. NX_KAWPOW_TUNE="copies=1,threads=256,minblocks=4".  Read once per process.
 struct Tune
 {
-    int copies = 8, threads = 1024, minblocks = 1, rotimad = 0, l1hi = 0, unroll = 1, ilv = 1;
+    int copies = 8, threads = 1024, minblocks = 1, rotimad = 0, l1hi = 0, unroll = 1, ilv = 1, daghint = 0;
     size_t smem_bytes() const { return (size_t)copies * 16384 + (size_t)14 * 4 * threads; }
     std::string tag() const
     {
         std::ostringstream s;
-        s << "c" << copies << "t" << threads << "b" << minblocks << "r" << rotimad << "h" << l1hi << "u" << unroll << "i" << ilv;
+        s << "c" << copies << "t" << threads << "b" << minblocks << "r" << rotimad << "h" << l1hi << "u" << unroll << "i" << ilv << "d" << daghint;
         return s.str();
     }
 };
@@ -110,6 +110,7 @@ const Tune& tune()
                 if (k == "l1hi" && v >= 0 && v <= 2) t.l1hi = v;
                 if (k == "unroll" && (v == 1 || v == 2 || v == 4 || v == 8)) t.unroll = v;
                 if (k == "ilv" && (v == 1 || v == 2)) t.ilv = v;
+                if (k == "daghint" && v >= 0 && v <= 3) t.daghint = v;
             }
             pos = end + 1;
         }
@@ -171,9 +172,10 @@ int compile_cubin(uint64_t prog_seed, uint32_t dag_items, std::vector<char>& cub
     const std::string d_hi = "-DNX_L1_HI=" + std::to_string(tn.l1hi);
     const std::string d_unroll = "-DNX_UNROLL=" + std::to_string(tn.unroll);
     const std::string d_ilv = "-DNX_ILV=" + std::to_string(tn.ilv);
+    const std::string d_hint = "-DNX_DAG_HINT=" + std::to_string(tn.daghint);
     std::vector<const char*> opts = {arch.c_str(), "--std=c++17", "-lineinfo", "--extra-device-vectorization",
                                      d_threads.c_str(), d_blocks.c_str(), d_copies.c_str(), d_rot.c_str(),
-                                     d_hi.c_str(), d_unroll.c_str(), d_ilv.c_str()};
+                                     d_hi.c_str(), d_unroll.c_str(), d_ilv.c_str(), d_hint.c_str()};
     std::vector<std::string> extra;
     if (const char* e = std::getenv("NX_KAWPOW_NVRTC_FLAGS")) {  // space separated, for experiments
         std::istringstream is(e);
