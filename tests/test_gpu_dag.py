@@ -1,6 +1,5 @@
 """K3 (DAG generation) / light cache / L1 cache parity on the GPU, through the C ABI.
 Bit-exact against the oracle, the reference-made fixtures and whole-DAG digests."""
-import ctypes as C
 import hashlib
 import random
 import struct

@@ -1,7 +1,6 @@
 """Node-side glue of the KawPow path against fixtures made by the reference's
 OWN block.cpp / hash.cpp / arith_uint256.cpp / uint256.cpp / chain.h (oracle/ref_node_shim.cpp -> tests/golden/
 node_glue.json), and against that code live where oracle/_ref/libnxref_node.so exists.  Host code only, no GPU."""
-import ctypes as C
 import os
 import random
 import struct
@@ -10,7 +9,6 @@ import pytest
 from conftest import golden
 
 from nodexa_chain_core_b200 import node
-from nodexa_chain_core_b200._lib import inb, lib, outb
 
 G = golden("node_glue.json")
 ACT = G["activation_time"]

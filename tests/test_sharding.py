@@ -3,8 +3,6 @@ the lowest-nonce reduction over world_size-2 `gloo` picks the right rank's hit."
 import os
 import socket
 
-import pytest
-
 from nodexa_chain_core_b200 import sharding
 
 
