@@ -61,6 +61,7 @@ class ClockSampler(threading.Thread):
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
                 parts = [x.strip() for x in out.strip().split(",")]
                 if len(parts) >= 7:
+                    float(parts[0]), float(parts[1])  # "[N/A]" on an odd driver: skip the sample instead of failing later
                     self.rows.append(parts)
             except Exception:
                 pass
