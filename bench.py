@@ -290,18 +290,36 @@ def main():
     for k in range(args.warmup):
         step_enqueue(k)
     progpow.search_sync(ctx)
-    sampler = ClockSampler(local)
-    barrier()
-    sampler.start()
-    w0 = time.perf_counter()
-    for k in range(args.steps):
-        step_enqueue(args.warmup + k)
-    sr = progpow.search_sync(ctx)
-    barrier()
-    wall_s = time.perf_counter() - w0
-    clocks = sampler.summary()
-    kernel_ms, launches = ctx.last_timing()
-    assert not sr.solution_found and launches == args.steps
+
+    def timed_pass(first_step):
+        sampler = ClockSampler(local)
+        barrier()
+        sampler.start()
+        w0 = time.perf_counter()
+        for k in range(args.steps):
+            step_enqueue(first_step + k)
+        res = progpow.search_sync(ctx)
+        barrier()
+        wall = time.perf_counter() - w0
+        clk = sampler.summary()
+        ms, n = ctx.last_timing()
+        assert not res.solution_found and n == args.steps
+        return ms, wall, clk
+
+    kernel_ms, wall_s, clocks = timed_pass(args.warmup)
+    launches = args.steps
+    # a pass that saw a hardware or thermal slowdown on ANY rank is thrown away and measured again, once
+    # (sw_power_cap is the board's normal state under this kernel: kept and reported)
+    bad = {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+    redo = torch.tensor([1.0 if bad & set(clocks["reasons"]) else 0.0], device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(redo, op=dist.ReduceOp.MAX)
+    first_attempt = None
+    if redo.item() > 0:
+        first_attempt = {"clocks": clocks, "kernel_ms": kernel_ms}
+        time.sleep(5.0)
+        kernel_ms, wall_s, clocks = timed_pass(args.warmup + args.steps)
+        launches += args.steps
 
     # ---- end to end through the C ABI with HOST buffers: header+boundary in, search_result out, per step ----
     e2e_steps = max(3, min(args.steps, 40))  # 3.4 s of end-to-end calls at the default step size
@@ -370,12 +388,13 @@ def main():
             "wall_ms_per_step": wall_ms / args.steps,
             "e2e": {"value": e2e_mhs, "unit": "MH/s", "h2d_bytes_per_step": 64 + 24 + 8, "d2h_bytes_per_step": 8,
                     "steps": e2e_steps, "api": "nx_kawpow_search (C ABI, host header/boundary in, search_result out)"},
-            "gpu_launches": args.steps + e2e_steps * ((B + (1 << 22) - 1) // (1 << 22)),
+            "gpu_launches": launches + e2e_steps * ((B + (1 << 22) - 1) // (1 << 22)),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_hash": DAG_BYTES_PER_HASH, "kernel": "nx_kawpow_kernel (search mode)",
                          "roofline_mhs": peak * 1e9 / DAG_BYTES_PER_HASH / 1e6},
             "clocks": clocks,
+            **({"rejected_first_attempt": first_attempt} if first_attempt else {}),
             "found_nonce_plumbing": plumbing,
             "epoch_build": {"light_cache_ms": light_ms, "dag_kernel_ms": dag_ms, "allgather_ms": allgather_ms,
                             "total_s": build_s, "dag_gbs_written": ctx.dag_bytes / world / (dag_ms * 1e-3) / 1e9},
