@@ -12,7 +12,7 @@ CXXSRC    := nx_host.cpp nx_codegen.cpp nx_kawpow_rt.cpp nx_abi.cpp nx_kernel_sr
 CUSRC     := nx_dag.cu nx_kawpow_interp.cu nx_equihash.cu
 OBJS      := $(addprefix $(OBJ)/,$(CXXSRC:.cpp=.o) $(CUSRC:.cu=.o)) $(OBJ)/nx_lightcache_avx512.o $(OBJ)/nx_cpu_dispatch.o
 
-.PHONY: all lib oracle ref clean
+.PHONY: all lib oracle ref clean ubench
 all: lib oracle
 
 lib: $(LIB)
@@ -46,6 +46,12 @@ $(LIB): $(OBJS)
 
 oracle:
 	$(MAKE) -C oracle oracle
+
+# stand-alone micro-benchmarks (tools/ubench): the measured ceilings DESIGN.md section 4 divides by
+ubench: build/nx_ubench
+build/nx_ubench: tools/ubench/nx_ubench.cu
+	@mkdir -p build
+	$(NVCC) $(ARCH) -O3 -lineinfo -std=c++17 -cudart static -o $@ $<
 
 ref: lib
 	$(MAKE) -C oracle ref ref_tests ref_node_dropin ref_node_explicit

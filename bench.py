@@ -333,10 +333,13 @@ def main():
         assert not r.solution_found
     barrier()
     e2e_s = time.perf_counter() - e0
+    e2e_launches = e2e_steps * ctx.last_timing()[1]
 
     # ---- found-nonce plumbing (not timed): a boundary that ~4 of 2^26 nonces meet; the hit must verify ----
     plumbing = None
-    if rank == 0:
+    tune_env = os.environ.get("NX_KAWPOW_TUNE", "")
+    measurement_only = any(k in tune_env for k in ("nodag=1", "nomath=1"))  # ceiling shapes: the hashes are not KawPow's
+    if rank == 0 and not measurement_only:
         easy = bytes.fromhex("000000ff" + "ff" * 28)
         hdp = header_for(7777, ethash.keccak256)
         sr_hit = progpow.search(ctx, height, hdp, easy, 7777 << 32, 1 << 26)
@@ -388,7 +391,7 @@ def main():
             "wall_ms_per_step": wall_ms / args.steps,
             "e2e": {"value": e2e_mhs, "unit": "MH/s", "h2d_bytes_per_step": 64 + 24 + 8, "d2h_bytes_per_step": 8,
                     "steps": e2e_steps, "api": "nx_kawpow_search (C ABI, host header/boundary in, search_result out)"},
-            "gpu_launches": launches + e2e_steps * ((B + (1 << 22) - 1) // (1 << 22)),
+            "gpu_launches": launches + e2e_launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_hash": DAG_BYTES_PER_HASH, "kernel": "nx_kawpow_kernel (search mode)",
@@ -396,6 +399,7 @@ def main():
             "clocks": clocks,
             **({"rejected_first_attempt": first_attempt} if first_attempt else {}),
             "found_nonce_plumbing": plumbing,
+            **({"measurement_only_shape": tune_env} if measurement_only else {}),
             "epoch_build": {"light_cache_ms": light_ms, "dag_kernel_ms": dag_ms, "allgather_ms": allgather_ms,
                             "total_s": build_s, "dag_gbs_written": ctx.dag_bytes / world / (dag_ms * 1e-3) / 1e9},
         }

@@ -12,14 +12,20 @@
 // Replaces: progpow::hash / search / verify, hash_mix, init_mix, round, random_math, random_merge
 // (reference src/crypto/ethash/lib/ethash/progpow.cpp:92-144,179-355,431-495,553-579).
 //
-// Work decomposition (one CTA = NX_THREADS threads = NX_THREADS nonces):
-//   * every thread absorbs its own nonce with keccak-f800 (25 words in registers);
-//   * the 16 threads of a half-warp then act as the 16 ProgPoW lanes and walk through their 16
-//     nonces one after the other: the seed is broadcast by shuffle, each lane keeps its 32 mix
-//     words in registers, the 256-byte DAG item of a round is fetched as sixteen coalesced
-//     16-byte loads (one per lane), the 16 KiB L1 cache sits in shared memory;
-//   * every thread finishes its own nonce with the second keccak-f800 and either stores
-//     {final, mix} (batch mode) or compares against the boundary (search mode).
+// Work decomposition (persistent CTAs: the grid is sized to the SM count and every WARP walks the job on its own):
+//   * the CTA stages the L1 cache in shared memory once (the only CTA-wide barrier), then each warp takes
+//     "units" of 2 x job.per_hw nonces - unit u, u + (warps in the grid), ... in ascending nonce order;
+//   * per unit every thread absorbs its own nonce with keccak-f800 (25 words in registers);
+//   * the 16 threads of a half-warp then act as the 16 ProgPoW lanes and walk through the half-warp's
+//     per_hw (normally 16) nonces one after the other: the seed is broadcast by shuffle, each lane keeps its
+//     32 mix words in registers, the 256-byte DAG item of a round is fetched as sixteen coalesced 16-byte
+//     loads (one per lane), the 16 KiB L1 cache sits in shared memory;
+//   * every thread finishes its own nonce with the second keccak-f800 and either stores {final, mix}
+//     (batch mode) or compares against the boundary (search mode).
+// Because warps are independent after the first barrier, the keccak phases (integer pipe only) of some warps
+// overlap the round loops (shared-memory pipe) of others, a search stops at the first unit that lies above an
+// already reported nonce (the reference returns at its first hit, progpow.cpp:572-577), and a small call
+// (per_hw < 16) is spread over all SMs instead of costing a full 16-nonce walk.
 
 typedef unsigned int u32;
 typedef unsigned long long u64;
@@ -52,9 +58,6 @@ typedef unsigned long long u64;
 #endif
 #ifndef NX_DAG_HINT
 #define NX_DAG_HINT 0  // cache hints on the DAG load (see nx_ld_dag)
-#endif
-#ifndef NX_ILV
-#define NX_ILV 1  // nonces a half-warp works on at the same time (1 or 2)
 #endif
 #ifndef NX_L1_HI
 #define NX_L1_HI 0
@@ -234,6 +237,8 @@ struct NxJob
     u32 mode;            // 0: store {final, mix} per nonce;  1: search (compare on device, atomicMin the offset)
     u32 l1_mul_lo;       // 2^20                      } NX_L1_HI == 2: L1 addressing multipliers handed over as kernel
     u32 l1_mul_hi;       // 2^(14 + log2 L1 replicas) } parameters, so that ptxas cannot fold the multiplies into ALU shifts
+    u32 per_hw;          // nonces a half-warp walks per unit, 1..16 (16 unless the call is too small to fill the GPU)
+    u32 n_units;         // ceil(count / (2 * per_hw)); unit u covers offsets [u * 2 * per_hw, (u + 1) * 2 * per_hw)
     u32 pad;
 };
 
@@ -287,6 +292,12 @@ NX_DEV uint4 nx_ld_dag(const uint4* p)
 // One kernel for both uses, so that a period costs ONE NVRTC compilation: job.mode 0 stores {final[8], mix[8]} per
 // nonce into `result` (u32[16] each), job.mode 1 atomicMins the offset of qualifying nonces into `result` (one u64).
 // The mode only decides what happens to the finished hash - a uniform branch after the last keccak.
+//
+// Measurement-only shapes (NX_KAWPOW_TUNE nodag=1 / nomath=1; results are NOT KawPow hashes):
+//   NX_NODAG   the round's DAG words are derived from the item index in registers instead of being loaded: index
+//              chain, L1 reads, math, merges, shuffles and both keccaks unchanged -> the on-chip ceiling of the kernel;
+//   NX_NOMATH  the 11 cache reads and 18 math ops are dropped, the index chain, the sixteen 16-byte loads per round and
+//              the four DAG merges stay -> what the dependent 256-byte reads alone achieve at this occupancy.
 extern "C" __global__ void __launch_bounds__(NX_THREADS, NX_MIN_BLOCKS)
 nx_kawpow_kernel(const uint4* __restrict__ dag, const NxJob job, void* __restrict__ result)
 {
@@ -305,8 +316,6 @@ nx_kawpow_kernel(const uint4* __restrict__ dag, const NxJob job, void* __restric
     // 32-bit shared-window address of word 0 of this lane's replica
     const u32 l1_base = (u32)__cvta_generic_to_shared(l1s) + l1_rep * 4u;
     const u32 lane = tid & 15u;
-    const u64 gid = (u64)blockIdx.x * NX_THREADS + tid;
-    const u64 nonce = job.start_nonce + gid;
 
     // L1 cache = first 16 KiB of the DAG (reference ethash.cpp:168-170)
 #if NX_L1_COPIES == 1
@@ -318,59 +327,63 @@ nx_kawpow_kernel(const uint4* __restrict__ dag, const NxJob job, void* __restric
         for (int g = 0; g < NX_L1_COPIES; ++g) l1s[i * NX_L1_COPIES + g] = v;
     }
 #endif
+    __syncthreads();  // the only CTA-wide barrier: carry_s / digest_s slots are private to their thread
 
-    u32 seed0, seed1;
-    {
-        u32 st[25];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) st[i] = job.header[i];
-        st[8] = (u32)nonce;
-        st[9] = (u32)(nonce >> 32);
-        NX_PAD_FIRST(st);
-        nxk_f800(st);
-        seed0 = st[0];
-        seed1 = st[1];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) carry_s[i][tid] = st[2 + i];
-    }
-    __syncthreads();
-
-    // NX_ILV == 2: the half-warp walks its 16 nonces two at a time, both mixes (2 x 32 words) live in registers and the
-    // two round programs are independent instruction streams.  A hash is a chain of 64 dependent DAG reads (each round's
-    // item index comes out of the previous round's DAG merge), so what one SM delivers is (hashes in flight) / (64 x
-    // DRAM latency); two hashes per thread share the non-mix registers and so put more hashes in flight per register file.
+    const u32 per_hw = job.per_hw;
+    const u32 unit_nonces = 2u * per_hw;
+    // The loop counter is built from launch-wide values only, so that the compiler can see that a warp never
+    // diverges here (a counter derived from threadIdx would cost a convergence check before every shuffle of the round
+    // loop).  A warp whose unit lies past the end still walks it - its results are dropped - and only in the last stripe.
 #pragma unroll 1
-    for (u32 h = 0; h < 16u; h += NX_ILV) {
-        u32 m[32];
-        nx_fill_mix(__shfl_sync(0xffffffffu, seed0, h, 16), __shfl_sync(0xffffffffu, seed1, h, 16), lane, m);
-#if NX_ILV == 2
-        u32 n[32];
-        nx_fill_mix(__shfl_sync(0xffffffffu, seed0, h + 1u, 16), __shfl_sync(0xffffffffu, seed1, h + 1u, 16), lane, n);
-#endif
-
-#pragma unroll NX_UNROLL
-        for (u32 r = 0; r < 64u; ++r) {
-            // item index comes from lane r%16 (reference progpow.cpp:182-183)
-            const u32 item = __shfl_sync(0xffffffffu, m[0], r & 15u, 16) % NX_DAG_ITEMS;
-            const uint4 d = nx_ld_dag(dag + ((u64)item * 16u + ((lane ^ r) & 15u)));
-#if NX_ILV == 2
-            const u32 item2 = __shfl_sync(0xffffffffu, n[0], r & 15u, 16) % NX_DAG_ITEMS;
-            const uint4 e = nx_ld_dag(dag + ((u64)item2 * 16u + ((lane ^ r) & 15u)));
-#endif
-#define NX_L1(x) nx_l1_load((x), l1_base, job.l1_mul_lo, job.l1_mul_hi)
-            NX_ROUND_CACHE_MATH(m, NX_L1);
-#if NX_ILV == 2
-            NX_ROUND_CACHE_MATH(n, NX_L1);
-#endif
-#undef NX_L1
-            NX_ROUND_DAG(m, d.x, d.y, d.z, d.w);
-#if NX_ILV == 2
-            NX_ROUND_DAG(n, e.x, e.y, e.z, e.w);
-#endif
+    for (u32 stripe = blockIdx.x * (NX_THREADS / 32u); stripe < job.n_units; stripe += gridDim.x * (NX_THREADS / 32u)) {
+        const u32 unit = stripe + (tid >> 5);
+        if (job.mode != 0u) {
+            // units ascend in nonce order within a warp: once a nonce below this unit has been reported, neither this
+            // unit nor any later one of this warp can lower the minimum
+            const u64 best = *static_cast<volatile const u64*>(result);
+            if (__any_sync(0xffffffffu, best < job.report_base + (u64)unit * unit_nonces)) break;
+        }
+        u32 seed0, seed1;
+        {
+            // offset of this thread's nonce; lanes >= per_hw of a half-warp hash a neighbour's nonce and drop the result
+            const u64 nonce = job.start_nonce + (u64)unit * unit_nonces + ((tid >> 4) & 1u) * per_hw + lane;
+            u32 st[25];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) st[i] = job.header[i];
+            st[8] = (u32)nonce;
+            st[9] = (u32)(nonce >> 32);
+            NX_PAD_FIRST(st);
+            nxk_f800(st);
+            seed0 = st[0];
+            seed1 = st[1];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) carry_s[i][tid] = st[2 + i];
         }
 
-        // 16 lane hashes -> 8 words (reference progpow.cpp:288-293)
-        {
+#pragma unroll 1
+        for (u32 h = 0; h < per_hw; ++h) {
+            u32 m[32];
+            nx_fill_mix(__shfl_sync(0xffffffffu, seed0, h, 16), __shfl_sync(0xffffffffu, seed1, h, 16), lane, m);
+
+#pragma unroll NX_UNROLL
+            for (u32 r = 0; r < 64u; ++r) {
+                // item index comes from lane r%16 (reference progpow.cpp:182-183)
+                const u32 item = __shfl_sync(0xffffffffu, m[0], r & 15u, 16) % NX_DAG_ITEMS;
+#ifdef NX_NODAG
+                const u32 di = item * 16u + ((lane ^ r) & 15u);
+                const uint4 d = make_uint4(di, di * 0x9E3779B1u, ~di, di + 0x7F4A7C15u);
+#else
+                const uint4 d = nx_ld_dag(dag + ((u64)item * 16u + ((lane ^ r) & 15u)));
+#endif
+#ifndef NX_NOMATH
+#define NX_L1(x) nx_l1_load((x), l1_base, job.l1_mul_lo, job.l1_mul_hi)
+                NX_ROUND_CACHE_MATH(m, NX_L1);
+#undef NX_L1
+#endif
+                NX_ROUND_DAG(m, d.x, d.y, d.z, d.w);
+            }
+
+            // 16 lane hashes -> 8 words (reference progpow.cpp:288-293)
             const u32 lh = nx_lane_reduce(m);
             u32 dg[8];
 #pragma unroll
@@ -382,52 +395,40 @@ nx_kawpow_kernel(const uint4* __restrict__ dag, const NxJob job, void* __restric
                 for (int i = 0; i < 8; ++i) digest_s[i][tid] = dg[i];
             }
         }
-#if NX_ILV == 2
-        {
-            const u32 lh = nx_lane_reduce(n);
-            u32 dg[8];
+        // digest_s[.][tid] was written by this very thread: no barrier needed
+
+        u32 st[25];
+        st[0] = seed0;
+        st[1] = seed1;
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
-                dg[i] = nx_fnv1a(nx_fnv1a(NX_FNV_BASIS, __shfl_sync(0xffffffffu, lh, i, 16)),
-                                 __shfl_sync(0xffffffffu, lh, i + 8, 16));
-            if (h + 1u == lane) {
+        for (int i = 0; i < 6; ++i) st[2 + i] = carry_s[i][tid];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) digest_s[i][tid] = dg[i];
+        for (int i = 0; i < 8; ++i) st[8 + i] = digest_s[i][tid];
+        NX_PAD_LAST(st);
+        nxk_f800(st);
+
+        const u64 gid = (u64)unit * unit_nonces + ((tid >> 4) & 1u) * per_hw + lane;
+        if (lane < per_hw && gid < job.count) {  // also false for a unit past the end (gid >= count)
+            if (job.mode == 0u) {
+                uint4* o = reinterpret_cast<uint4*>(static_cast<u32*>(result) + gid * 16u);
+                o[0] = make_uint4(st[0], st[1], st[2], st[3]);
+                o[1] = make_uint4(st[4], st[5], st[6], st[7]);
+                o[2] = make_uint4(digest_s[0][tid], digest_s[1][tid], digest_s[2][tid], digest_s[3][tid]);
+                o[3] = make_uint4(digest_s[4][tid], digest_s[5][tid], digest_s[6][tid], digest_s[7][tid]);
+            } else {
+                // final <= boundary as big-endian byte strings (reference ethash-internal.hpp:32-43)
+                bool ok = true;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const u32 a = nx_bswap(st[i]), b = job.boundary_be[i];
+                    if (a != b) {
+                        ok = a < b;
+                        break;
+                    }
+                }
+                if (ok) atomicMin(static_cast<u64*>(result), job.report_base + gid);
             }
         }
-#endif
-    }
-    // digest_s[.][tid] was written by this very thread: no barrier needed
-
-    u32 st[25];
-    st[0] = seed0;
-    st[1] = seed1;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) st[2 + i] = carry_s[i][tid];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) st[8 + i] = digest_s[i][tid];
-    NX_PAD_LAST(st);
-    nxk_f800(st);
-
-    if (gid >= job.count) return;
-    if (job.mode == 0u) {
-        uint4* o = reinterpret_cast<uint4*>(static_cast<u32*>(result) + gid * 16u);
-        o[0] = make_uint4(st[0], st[1], st[2], st[3]);
-        o[1] = make_uint4(st[4], st[5], st[6], st[7]);
-        o[2] = make_uint4(digest_s[0][tid], digest_s[1][tid], digest_s[2][tid], digest_s[3][tid]);
-        o[3] = make_uint4(digest_s[4][tid], digest_s[5][tid], digest_s[6][tid], digest_s[7][tid]);
-    } else {
-        // final <= boundary as big-endian byte strings (reference ethash-internal.hpp:32-43)
-        bool ok = true;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const u32 a = nx_bswap(st[i]), b = job.boundary_be[i];
-            if (a != b) {
-                ok = a < b;
-                break;
-            }
-        }
-        if (ok) atomicMin(static_cast<u64*>(result), job.report_base + gid);
     }
 }
 #endif  // __CUDACC__ && !NX_HELPERS_ONLY

@@ -14,7 +14,8 @@ using namespace nx;
 namespace
 {
 constexpr uint64_t NOT_FOUND = ~0ull;
-constexpr uint64_t SEARCH_BATCH = 1ull << 22;  // nonces per launch inside nx_kawpow_search
+constexpr uint64_t SEARCH_BATCH = 1ull << 26;  // nonces per launch inside nx_kawpow_search (0.34 s of work on a B200)
+constexpr int SEARCH_QUEUE = 8;                  // launches queued between two reads of the result
 
 inline uint32_t bswap32(uint32_t x) { return __builtin_bswap32(x); }
 
@@ -727,12 +728,21 @@ int nx_kawpow_search(const nx_epoch* c, int block_number, const uint8_t header_h
     // end wraps past 2^64 it is not above the start and nothing is scanned.  Same here.
     if (start_nonce + iterations <= start_nonce) return NX_OK;
     std::lock_guard<std::recursive_mutex> hold(const_cast<nx_epoch*>(c)->mu);
+    // Launches are queued SEARCH_QUEUE at a time and the result is read once per group: the kernel itself stops
+    // scanning above a reported nonce (every warp looks at the running minimum before each unit), so after a hit the
+    // launches still in the queue return at once and nothing is gained by a host round trip per launch.
     float total_ms = 0;
     int launches = 0;
-    for (uint64_t done = 0; done < iterations; done += SEARCH_BATCH) {
-        const uint64_t n = iterations - done < SEARCH_BATCH ? iterations - done : SEARCH_BATCH;
-        if ((rc = nx_kawpow_search_enqueue(c, block_number, header_hash, boundary, start_nonce + done, n)) != NX_OK)
-            return rc;
+    uint64_t done = 0;
+    while (done < iterations) {
+        for (int q = 0; q < SEARCH_QUEUE && done < iterations; ++q, done += SEARCH_BATCH) {
+            const uint64_t n = iterations - done < SEARCH_BATCH ? iterations - done : SEARCH_BATCH;
+            if ((rc = nx_kawpow_search_enqueue(c, block_number, header_hash, boundary, start_nonce + done, n)) != NX_OK) {
+                nx_search_result drop;
+                nx_kawpow_search_sync(c, &drop);  // leave no launch pending behind an error
+                return rc;
+            }
+        }
         if ((rc = nx_kawpow_search_sync(c, out)) != NX_OK) return rc;
         total_ms += c->last_kernel_ms;
         launches += c->last_launches;

@@ -76,8 +76,12 @@ struct KawpowJob
     uint64_t report_base;
     uint32_t mode;  // 0 batch hash, 1 search (set by the launch helpers)
     uint32_t l1_mul_lo, l1_mul_hi;  // L1 addressing multipliers for the NX_L1_HI == 2 shape (set by the launch helpers)
+    uint32_t per_hw, n_units;       // launch shape (set by the launch helpers, see kawpow_launch_shape)
     uint32_t pad;
 };
+static_assert(sizeof(KawpowJob) == 112, "KawpowJob must mirror NxJob in kawpow_kernel.cuh");
+void kawpow_launch_shape(uint64_t count, int threads, int sms, int minblocks, bool persist, uint32_t* per_hw,
+                         uint32_t* n_units, uint32_t* grid);
 struct KawpowProgram;  // one loaded module: (device, prog_seed, dag_items)
 int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items_256, std::shared_ptr<KawpowProgram>* out);
 int kawpow_compile_only(uint64_t prog_seed, uint32_t dag_items_256, std::vector<char>& cubin, std::string& log);

@@ -76,12 +76,16 @@ const char* cu_err(CUresult_ r)
 // NX_KAWPOW_TUNE overrides them, e.g. NX_KAWPOW_TUNE="copies=1,threads=256,minblocks=4".  Read once per process.
 struct Tune
 {
-    int copies = 8, threads = 1024, minblocks = 1, rotimad = 0, l1hi = 0, unroll = 1, ilv = 1, daghint = 0;
+    int copies = 8, threads = 1024, minblocks = 1, rotimad = 0, l1hi = 0, unroll = 1, daghint = 0;
+    int persist = 1;             // 1: grid = SMs x minblocks CTAs whose warps stride over the job; 0: one unit per warp
+    int nodag = 0, nomath = 0;   // measurement-only shapes (wrong hashes): see kawpow_kernel.cuh
     size_t smem_bytes() const { return (size_t)copies * 16384 + (size_t)14 * 4 * threads; }
     std::string tag() const
     {
         std::ostringstream s;
-        s << "c" << copies << "t" << threads << "b" << minblocks << "r" << rotimad << "h" << l1hi << "u" << unroll << "i" << ilv << "d" << daghint;
+        s << "c" << copies << "t" << threads << "b" << minblocks << "r" << rotimad << "h" << l1hi << "u" << unroll << "d" << daghint;
+        if (nodag) s << "ND";
+        if (nomath) s << "NM";
         return s.str();
     }
 };
@@ -109,7 +113,9 @@ const Tune& tune()
                 if (k == "rotimad" && v >= 0 && v <= 16) t.rotimad = v;
                 if (k == "l1hi" && v >= 0 && v <= 2) t.l1hi = v;
                 if (k == "unroll" && (v == 1 || v == 2 || v == 4 || v == 8)) t.unroll = v;
-                if (k == "ilv" && (v == 1 || v == 2)) t.ilv = v;
+                if (k == "persist" && (v == 0 || v == 1)) t.persist = v;
+                if (k == "nodag" && (v == 0 || v == 1)) t.nodag = v;
+                if (k == "nomath" && (v == 0 || v == 1)) t.nomath = v;
                 if (k == "daghint" && v >= 0 && v <= 3) t.daghint = v;
             }
             pos = end + 1;
@@ -123,7 +129,7 @@ std::string cache_path(uint64_t prog_seed, uint32_t dag_items, const char* arch)
     const char* dir = std::getenv("NX_PROGRAM_CACHE_DIR");
     if (!dir || !*dir) return "";
     std::ostringstream s;
-    s << dir << "/kawpow_" << arch << "_" << prog_seed << "_" << dag_items << "_" << tune().tag() << "_v3.cubin";
+    s << dir << "/kawpow_" << arch << "_" << prog_seed << "_" << dag_items << "_" << tune().tag() << "_v4.cubin";
     return s.str();
 }
 }  // namespace
@@ -138,6 +144,7 @@ struct KawpowProgram
     double compile_ms = 0;
     int regs = 0;
     int threads = 256;
+    int sms = 1;  // multiprocessors of the device: the persistent grid is sms x minblocks CTAs
     size_t smem_bytes = 0;
     ~KawpowProgram();
 };
@@ -171,11 +178,12 @@ int compile_cubin(uint64_t prog_seed, uint32_t dag_items, std::vector<char>& cub
     const std::string d_rot = "-DNX_ROT_IMAD=" + std::to_string(tn.rotimad);
     const std::string d_hi = "-DNX_L1_HI=" + std::to_string(tn.l1hi);
     const std::string d_unroll = "-DNX_UNROLL=" + std::to_string(tn.unroll);
-    const std::string d_ilv = "-DNX_ILV=" + std::to_string(tn.ilv);
     const std::string d_hint = "-DNX_DAG_HINT=" + std::to_string(tn.daghint);
     std::vector<const char*> opts = {arch.c_str(), "--std=c++17", "-lineinfo", "--extra-device-vectorization",
                                      d_threads.c_str(), d_blocks.c_str(), d_copies.c_str(), d_rot.c_str(),
-                                     d_hi.c_str(), d_unroll.c_str(), d_ilv.c_str(), d_hint.c_str()};
+                                     d_hi.c_str(), d_unroll.c_str(), d_hint.c_str()};
+    if (tn.nodag) opts.push_back("-DNX_NODAG=1");
+    if (tn.nomath) opts.push_back("-DNX_NOMATH=1");
     std::vector<std::string> extra;
     if (const char* e = std::getenv("NX_KAWPOW_NVRTC_FLAGS")) {  // space separated, for experiments
         std::istringstream is(e);
@@ -305,6 +313,7 @@ static int get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
         }
     }
     if (d.FuncGetAttribute) d.FuncGetAttribute(&p->regs, 4 /*CU_FUNC_ATTRIBUTE_NUM_REGS*/, p->fn);
+    NX_CUDA(cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, device));
     p->compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (std::getenv("NX_VERBOSE"))
         fprintf(stderr, "[nx] kawpow program seed=%llu items=%u tune=%s: %.1f ms, regs=%d smem=%zu\n",
@@ -333,10 +342,34 @@ int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
     return guarded([&] { return get_program(device, prog_seed, dag_items, out); });
 }
 
+// Shape of one launch.  A unit is the work one warp does between two looks at the job: 2 x per_hw nonces (one
+// half-warp walks per_hw of them).  per_hw is 16 unless the call is too small to give every resident warp a full unit:
+// then the nonces are spread thinner so that the call costs per_hw / 16 of a full walk instead of a whole one (a
+// 65 536-nonce call - the reference's nInnerLoopCount, src/rpc/mining.cpp:119 - gets per_hw = 7 on 148 SMs).
+void kawpow_launch_shape(uint64_t count, int threads, int sms, int minblocks, bool persist, uint32_t* per_hw,
+                         uint32_t* n_units, uint32_t* grid)
+{
+    const uint64_t warps_per_cta = (uint64_t)threads / 32;
+    const uint64_t resident_warps = (uint64_t)sms * minblocks * warps_per_cta;
+    uint64_t k = (count + 2 * resident_warps - 1) / (2 * resident_warps);
+    if (k < 1) k = 1;
+    if (k > 16) k = 16;
+    const uint64_t units = (count + 2 * k - 1) / (2 * k);
+    uint64_t ctas = (units + warps_per_cta - 1) / warps_per_cta;
+    if (persist && ctas > (uint64_t)sms * minblocks) ctas = (uint64_t)sms * minblocks;
+    *per_hw = (uint32_t)k;
+    *n_units = (uint32_t)units;
+    *grid = (uint32_t)ctas;
+}
+
 static int launch(const KawpowProgram* p, uint32_t mode, const void* dag, const KawpowJob& job_in, void* third,
                   cudaStream_t s)
 {
     if (job_in.count == 0) return NX_OK;
+    if (job_in.count > (1ull << 32)) {
+        set_error("kawpow launch: batch of %llu nonces is too large for one launch", (unsigned long long)job_in.count);
+        return NX_ERR_INVALID;
+    }
     KawpowJob job = job_in;
     job.mode = mode;
     int log_copies = 0;
@@ -344,13 +377,10 @@ static int launch(const KawpowProgram* p, uint32_t mode, const void* dag, const 
     job.l1_mul_lo = 1u << 20;
     job.l1_mul_hi = 1u << (14 + log_copies);
     job.pad = 0;
-    const uint64_t blocks = (job.count + p->threads - 1) / p->threads;
-    if (blocks > 0x7fffffffull) {
-        set_error("kawpow launch: batch of %llu nonces is too large for one grid", (unsigned long long)job.count);
-        return NX_ERR_INVALID;
-    }
+    uint32_t grid = 0;
+    kawpow_launch_shape(job.count, p->threads, p->sms, tune().minblocks, tune().persist != 0, &job.per_hw, &job.n_units, &grid);
     void* args[3] = {(void*)&dag, (void*)&job, (void*)&third};
-    const CUresult_ r = driver().LaunchKernel(p->fn, (unsigned)blocks, 1, 1, (unsigned)p->threads, 1, 1,
+    const CUresult_ r = driver().LaunchKernel(p->fn, grid, 1, 1, (unsigned)p->threads, 1, 1,
                                               (unsigned)p->smem_bytes, (void*)s, args, nullptr);
     if (r != 0) {
         set_error("cuLaunchKernel failed: %s", cu_err(r));

@@ -271,3 +271,59 @@ def test_other_epochs_live_vs_oracle(nx, oracle, epoch):
             assert ethash.hash(ctx, hd, n) == oracle.ethash_hash(epoch, hd, n)
     finally:
         ctx.close()
+
+
+def test_small_call_shapes_are_bit_exact(ctx_of, oracle):
+    """A call too small to give every resident warp 32 nonces is spread thinner (1..15 nonces per half-warp instead of
+    16, nx_kawpow_rt.cpp kawpow_launch_shape): every such shape must give the hashes of the full-size launch."""
+    ctx = ctx_of(0)
+    hd = hashlib.sha256(b"small-calls").digest()
+    start = 0xfeed00000000
+    big = progpow.hash_batch(ctx, 42, hd, start, 400000)  # 16 nonces per half-warp on any GPU up to 390 SMs
+    assert big[:6 * 64] == oracle.kawpow_hash_range(0, 42, hd, start, 6)
+    assert big[399990 * 64:] == oracle.kawpow_hash_range(0, 42, hd, start + 399990, 10)
+    for count in (1, 2, 3, 31, 32, 33, 4735, 4736, 4737, 9472, 9473, 18945, 30000, 65536, 66305, 131072, 151552, 151553, 303105):
+        assert progpow.hash_batch(ctx, 42, hd, start, count) == big[:count * 64], count
+    # search over the same small windows: lowest qualifying nonce, as a host scan of the batch output finds it
+    boundary = ((1 << (256 - 11)) - 1).to_bytes(32, "big")
+    finals = [big[i * 64:i * 64 + 32] for i in range(70000)]
+    hits = [i for i, f in enumerate(finals) if f <= boundary]
+    assert len(hits) > 8
+    for first, count in ((0, 65536), (hits[0] + 1, 9000), (hits[2] + 1, 70000 - hits[2] - 1), (hits[1], 1), (hits[1] + 1, hits[2] - hits[1] - 1)):
+        want = next((h for h in hits if first <= h < first + count), None)
+        sr = progpow.search(ctx, 42, hd, boundary, start + first, count)
+        assert sr.solution_found == (want is not None), (first, count)
+        if want is not None:
+            assert sr.nonce == start + want and sr.final_hash == finals[want]
+
+
+def test_search_stops_scanning_above_a_hit(ctx_of):
+    """The reference returns at its first hit (progpow.cpp:572-577).  The kernel's warps look at the running minimum
+    before each unit of work, so a hit near the start of a 2^26-nonce window (0.3 s of hashing) ends the call within
+    milliseconds, with the lowest qualifying nonce."""
+    ctx = ctx_of(0)
+    hd = hashlib.sha256(b"early-exit").digest()
+    start = 77 << 40
+    boundary = ((1 << (256 - 9)) - 1).to_bytes(32, "big")
+    head = progpow.hash_batch(ctx, 600, hd, start, 8192)
+    hits = [i for i in range(8192) if head[i * 64:i * 64 + 32] <= boundary]
+    assert hits, "no hit among 8192 nonces at 9 bits: change the header"
+    progpow.search(ctx, 600, hd, bytes(32), start, 1 << 20)  # warm: program loaded
+    progpow.search(ctx, 600, hd, bytes(32), start, 1 << 24)
+    full_ms, _ = ctx.last_timing()
+    sr = progpow.search(ctx, 600, hd, boundary, start, 1 << 26)
+    ms, launches = ctx.last_timing()
+    assert sr.solution_found and sr.nonce == start + hits[0]
+    assert ms < 5.0 and ms < full_ms, (ms, full_ms)
+    # several queued launches (2^28 nonces = 4 launches): the ones behind the hit return at once
+    sr = progpow.search(ctx, 600, hd, boundary, start, 1 << 28)
+    ms, launches = ctx.last_timing()
+    assert sr.solution_found and sr.nonce == start + hits[0] and ms < 5.0, (ms, launches)
+    # a hit in the LAST unit of a window is still found, and it is the lowest one
+    last = hits[-1]
+    first = max(0, last - 4095)
+    want = min(h for h in hits if h >= first)
+    sr = progpow.search(ctx, 600, hd, boundary, start + first, last - first + 1)
+    assert sr.solution_found and sr.nonce == start + want
+    sr = progpow.search(ctx, 600, hd, boundary, start + last, 1)
+    assert sr.solution_found and sr.nonce == start + last
