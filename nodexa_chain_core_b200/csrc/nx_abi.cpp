@@ -318,8 +318,14 @@ static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries;
     void* outs[NX_MAX_PEERS];
     int n = 0;
     outs[n++] = (char*)c->dag_dev + (size_t)first * 256;  // local copy first
-    for (int r = 0; r < c->world; ++r)
-        if (r != c->rank) outs[n++] = (char*)peer_bases[r] + (size_t)first * 256;
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank) continue;
+        if (!peer_bases[r]) {  // e.g. a rank whose context could not be created: never offset a null pointer
+            set_error("no DAG buffer given for rank %d", r);
+            return NX_ERR_INVALID;
+        }
+        outs[n++] = (char*)peer_bases[r] + (size_t)first * 256;
+    }
     std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
     {
@@ -378,6 +384,10 @@ int nx_epoch_finalize(nx_epoch* c)
         return NX_ERR_INVALID;
     }
     std::lock_guard<std::recursive_mutex> lk(c->mu);
+    if (c->deferred) {
+        set_error("this context's DAG slice has not been generated yet (nx_epoch_generate_fused_* comes first)");
+        return NX_ERR_STATE;
+    }
     NX_CUDA(cudaSetDevice(c->device));
     // KawPow addresses floor(n/2) 256-byte items; classic Ethash also reaches the odd last 128-byte item
     // n-1, i.e. the first half of 256-byte item floor(n/2): generate that one item behind the rest.

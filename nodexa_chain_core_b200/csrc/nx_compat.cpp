@@ -4,7 +4,11 @@
 //
 // Error behaviour follows the reference: no exceptions, no errno; create returns nullptr on failure
 // (ethash.cpp:147-148), verify returns false, search returns the all-zero result, find_epoch_number -1.
-// A failed device call inside hash() yields an all-zero result and leaves the reason in nx_last_error().
+// A failed device call inside hash() FAILS CLOSED: the reference's signature has no error channel, so the result is
+// {final_hash = ff..ff, mix_hash = ff..ff} - a final hash no boundary accepts and a mix no honest header carries -
+// and the reason stays in nx_last_error().  (An all-zero result would pass CheckProofOfWork for every nBits.)
+// With NX_COMPAT_ON_ERROR=abort the process stops instead, which is what the reference's CPU code amounts to when
+// it cannot continue.
 #include "../../include/nx/ethash_compat.hpp"
 #include "nx_internal.hpp"
 
@@ -41,6 +45,29 @@ ethash_epoch_context_full* create(int epoch) noexcept
     auto* c = new (std::nothrow) ethash_epoch_context_full(h);
     if (!c) nx_epoch_destroy(h);
     return c;
+}
+
+// What hash() hands back when the device call did not succeed (see the header comment).
+ethash::result failed_result() noexcept
+{
+    if (const char* e = std::getenv("NX_COMPAT_ON_ERROR"))
+        if (std::strcmp(e, "abort") == 0) {
+            std::fprintf(stderr, "libnxkawpow: hash failed: %s\n", nx_last_error());
+            std::abort();
+        }
+    ethash::result out;
+    std::memset(out.final_hash.bytes, 0xff, 32);
+    std::memset(out.mix_hash.bytes, 0xff, 32);
+    return out;
+}
+
+// test hook: NX_COMPAT_INJECT_FAIL=1 makes every compat hash() behave as if its device call had failed
+bool injected_failure() noexcept
+{
+    const char* e = std::getenv("NX_COMPAT_INJECT_FAIL");
+    if (!e || !*e || *e == '0') return false;
+    nx::set_error("injected failure (NX_COMPAT_INJECT_FAIL)");
+    return true;
 }
 
 ethash::result to_result(const nx_result& r) noexcept
@@ -102,8 +129,7 @@ const ethash_epoch_context_full* ethash_get_global_epoch_context_full(int e) noe
 ethash_result ethash_hash(const ethash_epoch_context* c, const ethash_hash256* header, uint64_t nonce) noexcept
 {
     nx_result r;
-    std::memset(&r, 0, sizeof r);
-    nx_ethash_hash(handle(*c), header->bytes, nonce, &r);
+    if (injected_failure() || nx_ethash_hash(handle(*c), header->bytes, nonce, &r) != NX_OK) return failed_result();
     return to_result(r);
 }
 
@@ -184,8 +210,7 @@ namespace progpow
 result hash(const epoch_context& c, int block_number, const hash256& header, uint64_t nonce) noexcept
 {
     nx_result r;
-    std::memset(&r, 0, sizeof r);
-    nx_kawpow_hash(handle(c), block_number, header.bytes, nonce, &r);
+    if (injected_failure() || nx_kawpow_hash(handle(c), block_number, header.bytes, nonce, &r) != NX_OK) return failed_result();
     return to_result(r);
 }
 result hash(const epoch_context_full& c, int block_number, const hash256& header, uint64_t nonce) noexcept

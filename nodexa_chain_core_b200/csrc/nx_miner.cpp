@@ -112,11 +112,18 @@ int build_contexts(const std::vector<int>& devices, int epoch, std::vector<nx_ep
         for (auto& t : th) t.join();  // doubles as the barrier between the phases
     };
     if (fused) {
+        // Every phase needs every rank: a slice that was not generated, or a buffer that does not exist, would leave
+        // holes in (or stray stores into) the DAGs of the healthy devices.  So one failure ends the build there.
+        auto any_failed = [&] {
+            for (size_t i = 0; i < n; ++i)
+                if (rcs[i] != NX_OK) return true;
+            return false;
+        };
         run_all([&](size_t i) { return nx_epoch_create_deferred(epoch, devices[i], (int)i, (int)n, light.data(), &out[i]); });
         std::vector<void*> bases(n, nullptr);
         for (size_t i = 0; i < n; ++i) bases[i] = out[i] ? nx_epoch_dag_ptr(out[i]) : nullptr;
-        run_all([&](size_t i) { return nx_epoch_generate_fused_peers(out[i], bases.data()); });
-        run_all([&](size_t i) { return nx_epoch_finalize(out[i]); });
+        if (!any_failed()) run_all([&](size_t i) { return nx_epoch_generate_fused_peers(out[i], bases.data()); });
+        if (!any_failed()) run_all([&](size_t i) { return nx_epoch_finalize(out[i]); });
     } else {
         run_all([&](size_t i) { return nx_epoch_create_from_light(epoch, devices[i], light.data(), &out[i]); });
     }
@@ -308,7 +315,7 @@ static int nx_miner_search_body(nx_miner* m, int block_number, const uint8_t hea
         if ((rc = nx_kawpow_prepare(c, block_number)) != NX_OK) return rc;
 
     const uint64_t B = m->batch;
-    const uint64_t total_batches = (iterations + B - 1) / B;
+    const uint64_t total_batches = iterations / B + (iterations % B != 0);  // no wrap for iterations near 2^64
     std::atomic<uint64_t> best_offset{~0ull};  // lowest hit so far, as an offset from start_nonce
     std::atomic<uint64_t> scanned{0};
     std::atomic<uint64_t> next_batch{0};       // windows are claimed in ascending order by whichever device is free

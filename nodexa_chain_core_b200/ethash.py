@@ -55,10 +55,13 @@ class EpochContext:
     distinguishes a light and a full context; on B200 both hold the resident DAG.
     """
 
-    def __init__(self, epoch_number: int, device: int = 0, rank: int = 0, world: int = 1, deferred: bool = False):
+    def __init__(self, epoch_number: int, device: int = 0, rank: int = 0, world: int = 1, deferred: bool = False,
+                 light_cache: bytes = None):
         h = C.c_void_p()
         if deferred:
-            check(lib.nx_epoch_create_deferred(epoch_number, device, rank, world, None, C.byref(h)))
+            # light_cache: the epoch's light cache if the caller already has it (one serial chain for several contexts)
+            lc = C.cast(C.c_char_p(light_cache), C.c_void_p) if light_cache is not None else None
+            check(lib.nx_epoch_create_deferred(epoch_number, device, rank, world, lc, C.byref(h)))
         elif world == 1:
             check(lib.nx_epoch_create(epoch_number, device, C.byref(h)))
         else:
@@ -128,6 +131,11 @@ class EpochContext:
         """handles_by_rank: list of `world` 64-byte blobs from every rank's ipc_handle() (own entry ignored)."""
         blob = b"".join(handles_by_rank)
         check(lib.nx_epoch_generate_fused_ipc(self._h, inb(blob)))
+
+    def generate_fused_peers(self, dag_ptrs_by_rank) -> None:
+        """dag_ptrs_by_rank: `world` device pointers (dag_ptr of every rank's context in THIS process; own entry ignored)."""
+        arr = (C.c_void_p * len(dag_ptrs_by_rank))(*[C.c_void_p(p) for p in dag_ptrs_by_rank])
+        check(lib.nx_epoch_generate_fused_peers(self._h, arr))
 
     def finalize(self):
         """After the caller's in-place all-gather of a sharded DAG."""

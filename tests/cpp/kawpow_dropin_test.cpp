@@ -15,6 +15,7 @@
 #include <vector>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <string>
 
 static int failures = 0;
@@ -162,6 +163,32 @@ static void managed_threads()
     CHECK(bad.load() == 0);
 }
 
+// The reference's hash() has no error channel.  When the device call underneath fails, the drop-in must not hand the
+// node a result that validates: final_hash = ff..ff is above every boundary (CheckProofOfWork fails for any nBits),
+// mix_hash = ff..ff matches no honest header, and verify() says no.
+static void hash_fails_closed()
+{
+    const auto& ctx = ethash::get_global_epoch_context(0);
+    const auto h = to_hash256(kats[0].header);
+    const auto good = progpow::hash(ctx, 0, h, 0);
+    const ethash::hash256 easiest = to_hash256("ffffffffffffffffffffffffffffffffffffffffffffffffffffffffffffff00");
+    auto check_closed = [&](const ethash::result& r) {
+        bool all_ff = true;
+        for (int i = 0; i < 32; ++i) all_ff = all_ff && r.final_hash.bytes[i] == 0xff && r.mix_hash.bytes[i] == 0xff;
+        CHECK(all_ff);
+        CHECK(std::memcmp(r.final_hash.bytes, easiest.bytes, 32) > 0);
+    };
+    check_closed(progpow::hash(ctx, -1, h, 0));  // a block number the library refuses
+    setenv("NX_COMPAT_INJECT_FAIL", "1", 1);     // stands for OOM, a sticky CUDA error, an NVRTC failure ...
+    check_closed(progpow::hash(ctx, 0, h, 0));
+    check_closed(ethash::hash(ctx, h, 0));
+    CHECK(!ethash::verify(ctx, h, ethash::hash256{}, 0, easiest));
+    unsetenv("NX_COMPAT_INJECT_FAIL");
+    const auto again = progpow::hash(ctx, 0, h, 0);
+    CHECK(again.final_hash == good.final_hash && again.mix_hash == good.mix_hash);
+    CHECK(!progpow::verify(ctx, -1, h, good.mix_hash, 0, easiest));
+}
+
 int main()
 {
     kawpow_l1_cache();
@@ -171,6 +198,7 @@ int main()
     kawpow_search();
     managed_and_classic();
     managed_threads();
+    hash_fails_closed();
     if (failures) {
         std::printf("%d CHECK(s) FAILED\n", failures);
         return 1;

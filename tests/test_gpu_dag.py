@@ -162,3 +162,60 @@ def test_contexts_give_all_device_memory_back(nx, gpu):
             assert m.search(height, hd, b"\xff" * 32, 0, 1).solution_found
         m.wait_prepared()
     assert abs(free_bytes() - base) <= (8 << 20), (base, free_bytes())
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_fused_exchange_on_one_device_gives_the_reference_dag(nx, world):
+    """The fused multi-GPU build (every rank's K3 stores its slice into the DAG buffer of EVERY rank) with all `world`
+    ranks on cuda:0 - a pointer on the same device is a valid "peer" - so that the path is pinned on a 1-GPU box:
+    every rank's whole DAG must carry the reference-computed digest (ethash.cpp:209-251 item by item)."""
+    want = golden("dag_digest.json")["0"]["weighted_sum"]
+    first = nx.EpochContext(0, 0, rank=0, world=world, deferred=True)
+    ctxs = [first]
+    try:
+        light = first.light_cache
+        ctxs += [nx.EpochContext(0, 0, rank=r, world=world, deferred=True, light_cache=light) for r in range(1, world)]
+        with pytest.raises(nx.NxError):  # nothing generated yet: finalize must refuse instead of marking the DAG ready
+            ctxs[0].finalize()
+        ptrs = [c.dag_ptr for c in ctxs]
+        holes = list(ptrs)
+        holes[world - 1] = 0
+        with pytest.raises(nx.NxError):  # a rank without a buffer: refused, no store through a null pointer
+            ctxs[0].generate_fused_peers(holes)
+        for c in ctxs:
+            c.generate_fused_peers(ptrs)
+        for c in ctxs:
+            c.finalize()
+        for c in ctxs:
+            assert c.checksum() == want, c.rank
+        with pytest.raises(nx.NxError):  # a second generation on a finished context is a state error
+            ctxs[0].generate_fused_peers(ptrs)
+        kat = golden("kawpow_kats.json")["hash_cases"][0]
+        r = nx.progpow.hash(ctxs[world - 1], kat["height"], bytes.fromhex(kat["header"]), kat["nonce"])
+        assert r.final_hash.hex() == kat["final"] and r.mix_hash.hex() == kat["mix"]
+    finally:
+        for c in ctxs:
+            c.close()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_sharded_slices_copied_together_give_the_reference_dag(nx, world):
+    """The other exchange route (nx_epoch_create_sharded + an in-place all-gather, NCCL in production) with the gather
+    done by device-to-device copies on cuda:0: rank 0's buffer, completed with every other rank's slice, has the digest."""
+    import torch
+    want = golden("dag_digest.json")["0"]["weighted_sum"]
+    c0 = nx.EpochContext(0, 0, rank=0, world=world)
+    try:
+        dag0 = c0.dag_tensor()
+        share = c0.dag_share_bytes
+        for r in range(1, world):
+            c = nx.EpochContext(0, 0, rank=r, world=world)
+            try:
+                dag0[r * share:(r + 1) * share].copy_(c.dag_tensor()[r * share:(r + 1) * share])
+                torch.cuda.synchronize()
+            finally:
+                c.close()
+        c0.finalize()
+        assert c0.checksum() == want
+    finally:
+        c0.close()

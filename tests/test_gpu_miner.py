@@ -178,3 +178,16 @@ def test_chain_across_period_switches_and_an_epoch_boundary(nx, oracle):
         assert nxt.prev_block == h.block_hash() == sr.final_hash[::-1]
     for h, sr in headers[::5]:
         assert oracle.kawpow_hash(h.height // 7500, h.height, h.kawpow_header_hash(), h.nonce64) == (sr.final_hash, sr.mix_hash)
+
+
+def test_unbounded_try_count_scans_until_the_hit(nx):
+    """max_tries = 2^64 - 1 is a natural "no limit": the window count must not wrap to zero (it once did), the scan
+    starts at start_nonce and stops at the first qualifying nonce."""
+    hd = hashlib.sha256(b"no-limit").digest()
+    boundary = ((1 << (256 - 10)) - 1).to_bytes(32, "big")
+    with nx.Miner([0]) as m:
+        m.set_batch(1 << 16)
+        want = m.search(0, hd, boundary, 1, 1 << 20)
+        assert want.solution_found
+        got = m.search(0, hd, boundary, 1, 2**64 - 2)  # start + iterations stays below 2^64: the reference's loop runs
+        assert got == want
