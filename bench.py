@@ -171,6 +171,86 @@ def cpu_equihash_baseline(nonces: int = 2):
             "sol_per_s": sols / dt, "s_per_nonce": dt / nonces}
 
 
+def secondary_paths(nx, ctx, epoch, height, devices, peak_gbs):
+    """The other kernels of the path, a few seconds in all, after the timed region (rank 0): K3 DAG generation, K6
+    interpreted per-record hash, K7 classic Ethash, the single-process miner over `devices`, and the gated Equihash
+    engine.  Every rate is from CUDA events on the launching stream unless it says wall."""
+    import random
+
+    import torch
+
+    from nodexa_chain_core_b200 import ethash, progpow
+    out = {}
+    dev = ctx.device
+    # K3, whole DAG regenerated into a scratch buffer, warm
+    buf = torch.empty(ctx.dag_bytes, dtype=torch.uint8, device=f"cuda:{dev}")
+    ms = min(ctx.generate_range(0, ctx.dag_num_items, buf.data_ptr()) or ctx.last_timing()[0] for _ in range(2))
+    del buf
+    gather = ctx.dag_bytes // 64 * 512 * 64  # 512 parents of 64 B per 64-byte item (ethash.cpp:209-233 with 512 rounds)
+    k3 = {"ms": ms, "write_gbs": ctx.dag_bytes / ms / 1e6, "l2_gather_tbs": gather / ms / 1e9}
+    ub = os.path.join(ROOT, "build", "nx_ubench")
+    if os.path.exists(ub):
+        try:
+            g = json.loads(subprocess.run([ub, "gather"], capture_output=True, text=True, timeout=120).stdout)["gather"]
+            peak = max(v["tb_per_s"] for k, v in g.items() if k.startswith("inflight_"))
+            k3.update(l2_gather_peak_tbs=peak, frac_of_gather_peak=k3["l2_gather_tbs"] / peak,
+                      peak_source="tools/ubench gather: random 64-byte reads over a 72 MiB table, best of 1/4/8 in flight")
+        except Exception as e:  # noqa: BLE001
+            k3["l2_gather_peak_tbs"] = None
+            k3["peak_error"] = repr(e)[:120]
+    out["K3_dag_items_kernel"] = k3
+    # K6: independent records, nearly every one its own ProgPoW period
+    rnd = random.Random(1)
+    recs = [(height + rnd.randrange(7500), rnd.randbytes(32), rnd.getrandbits(64)) for _ in range(1 << 14)]
+    progpow.hash_many(ctx, recs[:64])
+    progpow.hash_many(ctx, recs)
+    kms, _ = ctx.last_timing()
+    out["K6_kawpow_interp_kernel"] = {"records": len(recs), "distinct_periods": len({r[0] // 3 for r in recs}),
+                                      "kernel_ms": kms, "mhs": len(recs) / kms / 1e3}
+    # K7: classic Ethash, 8 KiB of DAG per hash
+    hd = ethash.keccak256(b"paths")
+    ethash.hash_batch(ctx, hd, 0, 1 << 12)
+    ethash.hash_batch(ctx, hd, 1 << 32, 1 << 20)
+    kms, _ = ctx.last_timing()
+    roof = peak_gbs * 1e9 / 8192 / 1e6
+    out["K7_ethash_hash_kernel"] = {"nonces": 1 << 20, "mhs": (1 << 20) / kms / 1e3, "roofline_mhs": roof,
+                                    "frac": (1 << 20) / kms / 1e3 / roof}
+    # the single-process miner (what a node links), wall clock of the whole call
+    try:
+        with nx.Miner(devices) as m:
+            t0 = time.perf_counter()
+            m.set_epoch(epoch)
+            build = time.perf_counter() - t0
+            m.set_batch(1 << 24)
+            n = m.device_count
+            m.search(height, hd, bytes(32), 0, n << 22)
+            m.search(height, hd, bytes(32), 1 << 40, n << 26)
+            hashes, secs = m.last_stats()
+            out["nx_miner_search"] = {"devices": n, "mhs_wall": hashes / secs / 1e6, "nonces": hashes, "epoch_build_s": build}
+    except Exception as e:  # noqa: BLE001
+        out["nx_miner_search"] = {"error": repr(e)[:200]}
+    # gated Equihash engine: self-consistency only
+    try:
+        import hashlib
+        base = hashlib.sha512(b"nodexa-equihash-bench").digest() * 3
+        runs = []
+        for n_, k_, nonces in ((200, 9, 32), (144, 5, 8)):
+            with nx.equihash.Solver(n_, k_, b"NodexaPW") as sv:
+                sv.solve(base[:108] + (10**6).to_bytes(32, "little"))
+                sols, kms, dropped = 0, 0.0, 0
+                for i in range(nonces):
+                    sols += len(sv.solve(base[:108] + i.to_bytes(32, "little")))
+                    kms += sv.last_timing()[0]
+                    dropped += sv.last_dropped
+                runs.append({"n": n_, "k": k_, "nonces": nonces, "solutions": sols, "sol_per_s": sols / (kms * 1e-3),
+                             "ms_per_nonce": kms / nonces, "rows_dropped": dropped})
+        out["equihash_gated"] = {"runs": runs, "parity": "self-consistency only, not checked against the reference: "
+                                 "the reference defines no Equihash (no (n,k), personalization, validator or header field)"}
+    except Exception as e:  # noqa: BLE001
+        out["equihash_gated"] = {"error": repr(e)[:200]}
+    return out
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -212,6 +292,8 @@ def main():
     ap.add_argument("--dag-exchange", default="fused", choices=["fused", "nccl"],
                     help="N>1: how the DAG slices reach every GPU - peer stores inside the generating kernel, or NCCL")
     ap.add_argument("--no-full-dag-baseline", action="store_true")
+    ap.add_argument("--no-paths", action="store_true", help="skip the secondary kernels (K3, K6, K7, miner, Equihash) after the timed region")
+    ap.add_argument("--no-second-build", action="store_true", help="N>1: do not also build the epoch by the other exchange route")
     ap.add_argument("--cpu-baseline-extras", action="store_true",
                     help="also time the reference's epoch build on the host cores and the gated Equihash engine's CPU oracle")
     args = ap.parse_args()
@@ -239,36 +321,92 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
 
     epoch, height = args.epoch, args.epoch * 7500
-    # ---- epoch context: light cache + DAG.  N>1: each rank builds 1/N of the DAG, one in-place all-gather ----
-    t0 = time.perf_counter()
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def build_epoch(exchange):
+        """Epoch context for this rank.  N>1: ONE serial light-cache chain (rank 0) while every rank allocates, trades IPC
+        handles and maps its peers; the 72 MiB light cache is then broadcast and each rank generates 1/N of the DAG,
+        either storing it into every rank's buffer from inside the kernel ("fused") or into its own, followed by one
+        in-place NCCL all-gather ("nccl").  Returns (context, phases in ms)."""
+        ph = {}
+        t0 = time.perf_counter()
+        if world == 1:
+            c = nx.EpochContext(epoch, local)
+            ph["light_cache_ms"], ph["dag_kernel_ms"] = c.build_times_ms()
+            ph.update(exchange=None, allgather_ms=None, total_s=time.perf_counter() - t0)
+            return c, ph
+        c = nx.EpochContext(epoch, local, rank=rank, world=world, shell=True)
+        ph["alloc_ms"] = 1e3 * (time.perf_counter() - t0)
+        chain = None
+        if rank == 0:  # ctypes releases the GIL: the chain runs beside this rank's share of the set-up below
+            chain = threading.Thread(target=c.build_light_cache)
+            chain.start()
+        t1 = time.perf_counter()
+        if exchange == "fused":
+            handles = [None] * world
+            dist.all_gather_object(handles, c.ipc_handle())
+            c.open_ipc_peers(handles)
+        ph["ipc_setup_ms"] = 1e3 * (time.perf_counter() - t1)
+        if chain is not None:
+            chain.join()
+        t2 = time.perf_counter()
+        dist.broadcast(c.light_tensor(), src=0)  # also the point where the other ranks wait for the chain
+        torch.cuda.synchronize()
+        if rank != 0:
+            c.adopt_light_cache()
+        ph["light_wait_and_broadcast_ms"] = 1e3 * (time.perf_counter() - t2)
+        ph["allgather_ms"] = None
+        if exchange == "fused":
+            c.generate_fused_ipc(None)  # K3 stores this rank's slice into every rank's DAG buffer over NVLink
+            t3 = time.perf_counter()
+            sync_all()
+            ph["barrier_ms"] = 1e3 * (time.perf_counter() - t3)
+        else:
+            c.generate_slice()
+            dag = c.dag_tensor()
+            share = c.dag_share_bytes
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t3 = time.perf_counter()
+            sync_all()
+            ph["barrier_ms"] = 1e3 * (time.perf_counter() - t3)
+            e0.record()
+            dist.all_gather_into_tensor(dag, dag[rank * share:(rank + 1) * share])
+            e1.record()
+            torch.cuda.synchronize()
+            ph["allgather_ms"] = e0.elapsed_time(e1)
+            ph["allgather_gbs_received_per_gpu"] = (world - 1) * share / (ph["allgather_ms"] * 1e-3) / 1e9
+        c.finalize()
+        ph["light_cache_ms"], ph["dag_kernel_ms"] = c.build_times_ms()
+        ph.update(exchange=exchange, total_s=time.perf_counter() - t0)
+        return c, ph
+
+    # ---- epoch context: light cache + DAG ----
     fused = world > 1 and args.dag_exchange == "fused"
-    ctx = nx.EpochContext(epoch, local, rank=rank, world=world, deferred=fused)
-    light_ms, dag_ms = ctx.build_times_ms()
-    allgather_ms = 0.0
-    if fused:
-        handles = [None] * world
-        dist.all_gather_object(handles, ctx.ipc_handle())
-        torch.cuda.synchronize()
-        dist.barrier()
-        ctx.generate_fused_ipc(handles)  # K3 stores this rank's slice into every rank's DAG buffer over NVLink
-        torch.cuda.synchronize()
-        dist.barrier()
-        ctx.finalize()
-        light_ms, dag_ms = ctx.build_times_ms()
-    elif world > 1:
-        dag = ctx.dag_tensor()
-        share = ctx.dag_share_bytes
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        dist.barrier()
-        e0.record()
-        dist.all_gather_into_tensor(dag, dag[rank * share:(rank + 1) * share])
-        e1.record()
-        torch.cuda.synchronize()
-        allgather_ms = e0.elapsed_time(e1)
-        ctx.finalize()
-    build_s = time.perf_counter() - t0
+    ctx, build = build_epoch(args.dag_exchange)
+    build_s, light_ms, dag_ms = build["total_s"], build["light_cache_ms"], build["dag_kernel_ms"]
+    allgather_ms = build["allgather_ms"] or 0.0
     checksum = ctx.checksum()
+    # the whole DAG against the digest the reference's code produced (tests/golden/dag_digest.json), on every rank
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "dag_digest.json")) as f:
+            want_digest = json.load(f).get(str(epoch), {}).get("weighted_sum")
+    except OSError:
+        want_digest = None
+    if want_digest is not None:
+        assert checksum == want_digest, f"rank {rank}: DAG checksum {checksum} != reference digest {want_digest}"
+    # N>1: the other exchange route once more, off the clock of everything else, so that both have a number
+    other_build = None
+    if world > 1 and not args.no_second_build:
+        other, other_build = build_epoch("nccl" if fused else "fused")
+        assert other.checksum() == checksum, "the two exchange routes built different DAGs"
+        other.close()
+        del other
+        sync_all()
 
     boundary = bytes(32)  # nothing qualifies: the kernel scans every nonce of the batch
     B = args.batch
@@ -280,11 +418,7 @@ def main():
         start = ((1 << 32) + (k * world + rank) * B) & (2**64 - 1)
         progpow.search_enqueue(ctx, height, hd, boundary, start, B)
 
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-            torch.cuda.synchronize()
+    barrier = sync_all
 
     # ---- device-resident throughput: K kernels back to back, CUDA events on the launching stream ----
     for k in range(args.warmup):
@@ -351,7 +485,29 @@ def main():
                                         and progpow.hash_no_verify(height, hdp, sr_hit.mix_hash, sr_hit.nonce) == sr_hit.final_hash)
             assert plumbing["verified"], "a found nonce failed verification"
 
+    paths = None
+    if rank == 0 and not args.no_paths and not measurement_only:
+        try:
+            paths = secondary_paths(nx, ctx, epoch, height, list(range(world)), measured_peak_gbs()[0])
+        except Exception as e:  # noqa: BLE001 - an extra must never sink the bench line
+            paths = {"error": repr(e)[:300]}
+
     # ---- max over ranks ----
+    def max_over_ranks(ph):
+        """Per-phase times of an epoch build: the slowest rank's value for each key (None and strings pass through)."""
+        if ph is None:
+            return None
+        keys = sorted(k for k, v in ph.items() if isinstance(v, (int, float)) and not isinstance(v, bool))
+        v = torch.tensor([float(ph[k]) for k in keys], dtype=torch.float64, device=f"cuda:{local}")
+        if dist is not None:
+            dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        out = dict(ph)
+        out.update({k: x for k, x in zip(keys, v.tolist())})
+        return out
+
+    build = max_over_ranks(build)
+    other_build = max_over_ranks(other_build)
+    build_s = build["total_s"]
     t = torch.tensor([kernel_ms, e2e_s * 1e3, wall_s * 1e3, dag_ms, light_ms, allgather_ms], dtype=torch.float64,
                      device=f"cuda:{local}")
     cs = torch.tensor([checksum & 0x7fffffffffffffff], dtype=torch.int64, device=f"cuda:{local}")
@@ -399,9 +555,12 @@ def main():
             "clocks": clocks,
             **({"rejected_first_attempt": first_attempt} if first_attempt else {}),
             "found_nonce_plumbing": plumbing,
+            **({"paths": paths} if paths else {}),
             **({"measurement_only_shape": tune_env} if measurement_only else {}),
-            "epoch_build": {"light_cache_ms": light_ms, "dag_kernel_ms": dag_ms, "allgather_ms": allgather_ms,
-                            "total_s": build_s, "dag_gbs_written": ctx.dag_bytes / world / (dag_ms * 1e-3) / 1e9},
+            # per phase, slowest rank each; allgather_ms is null on the fused route (the exchange is inside dag_kernel_ms)
+            "epoch_build": {**build, "dag_gbs_written": ctx.dag_bytes / world / (dag_ms * 1e-3) / 1e9,
+                            "dag_checksum_equals_reference_digest": want_digest is not None,
+                            **({"other_route": other_build} if other_build else {})},
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1

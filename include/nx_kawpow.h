@@ -91,7 +91,22 @@ void nx_epoch_destroy(nx_epoch* ctx);
  *   3. barrier across ranks (every kernel has finished), then nx_epoch_finalize() on each. */
 int nx_epoch_create_deferred(int epoch, int device, int rank, int world, const uint8_t* light_cache, nx_epoch** out);
 int nx_epoch_ipc_handle(const nx_epoch* ctx, uint8_t handle[64]);
-int nx_epoch_generate_fused_ipc(nx_epoch* ctx, const uint8_t* handles_by_rank /* world x 64 bytes */);
+int nx_epoch_generate_fused_ipc(nx_epoch* ctx, const uint8_t* handles_by_rank /* world x 64 bytes; NULL once opened */);
+/* One serial chain for a whole multi-process job (build_light_cache, ethash.cpp:101-129, cannot be split: every rank
+ * running it redundantly makes an N-GPU epoch build SLOWER than a 1-GPU one).  Every rank creates a shell (allocations
+ * only) and, while the root rank runs nx_epoch_build_light_cache(), trades IPC handles and maps its peers with
+ * nx_epoch_open_ipc_peers(); the root's light cache is then broadcast in place into nx_epoch_light_ptr() of the others
+ * (ncclBroadcast / torch.distributed.broadcast, nx_epoch_light_items() x 64 bytes), which call
+ * nx_epoch_adopt_light_cache(); nx_epoch_generate_fused_ipc(ctx, NULL), a barrier and nx_epoch_finalize() follow. */
+int nx_epoch_create_shell(int epoch, int device, int rank, int world, nx_epoch** out);
+int nx_epoch_build_light_cache(nx_epoch* ctx);
+void* nx_epoch_light_ptr(const nx_epoch* ctx);        /* DEVICE pointer to the light cache */
+int nx_epoch_adopt_light_cache(nx_epoch* ctx);
+int nx_epoch_open_ipc_peers(nx_epoch* ctx, const uint8_t* handles_by_rank /* world x 64 bytes */);
+/* A shell (or deferred) context on the NCCL route: generate this rank's slice at its final offset in the own buffer;
+ * the caller's in-place all-gather of nx_epoch_dag_ptr() and nx_epoch_finalize() follow, as after
+ * nx_epoch_create_sharded(). */
+int nx_epoch_generate_slice(nx_epoch* ctx);
 int nx_epoch_generate_fused_peers(nx_epoch* ctx, void* const* peer_dag_ptrs /* world entries */);
 
 /* Public fields of the reference's struct ethash_epoch_context (ethash.h:35-42). */
@@ -130,12 +145,14 @@ int nx_dag_checksum(const nx_epoch* ctx, uint64_t* out);
  *
  *   data_device  device memory of the CURRENT device, 8-byte aligned (e.g. nx_epoch_dag_ptr())
  *   n_bytes      multiple of 8, at most NX_NOALLOC_MAX_BYTES (larger inputs are refused with
- *                NX_ERR_INVALID and a message; use nx_dag_checksum for those)
+ *                NX_ERR_INVALID and a message; use nx_dag_checksum for those); a range that runs past the
+ *                end of the allocation data_device points into is refused too, where the driver can tell
  *   stream       cudaStream_t to run on (NULL = default stream); the call returns after it completed
  *   out_host     receives the sum (same value as nx_dag_checksum over the same bytes)
  *
  * The first call on each device looks up the device address of the array (one-time set-up), so make
- * that first call before starting any stream capture on that device.  All calls share the one
+ * that first call before starting any stream capture on that device (after a cudaDeviceReset the next
+ * call repeats the look-up, so the same holds for it).  All calls share the one
  * array and it keeps whatever the previous call left in it; nothing in it needs to be zero at entry
  * (every slot is rewritten before it is read), but two calls that overlap on the same GPU - from two
  * threads or two streams - race on it: serialise them. */

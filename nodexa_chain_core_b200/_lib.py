@@ -80,6 +80,12 @@ def _load() -> C.CDLL:
         "nx_epoch_ipc_handle": (i, [vp, u8p]),
         "nx_epoch_generate_fused_ipc": (i, [vp, u8p]),
         "nx_epoch_generate_fused_peers": (i, [vp, C.POINTER(vp)]),
+        "nx_epoch_create_shell": (i, [i, i, i, i, C.POINTER(vp)]),
+        "nx_epoch_build_light_cache": (i, [vp]),
+        "nx_epoch_light_ptr": (vp, [vp]),
+        "nx_epoch_adopt_light_cache": (i, [vp]),
+        "nx_epoch_open_ipc_peers": (i, [vp, u8p]),
+        "nx_epoch_generate_slice": (i, [vp]),
         "nx_epoch_destroy": (None, [vp]),
         "nx_epoch_number": (i, [vp]),
         "nx_epoch_light_items": (i, [vp]),
@@ -107,6 +113,7 @@ def _load() -> C.CDLL:
         "nx_kawpow_verify": (i, [vp, i, u8p, u8p, u64, u8p]),
         "nx_kawpow_hash_no_verify": (None, [i, u8p, u8p, u64, u8p]),
         "nx_kawpow_hash_many": (i, [vp, C.POINTER(NxHashRecord), sz, vp]),
+        "nx_test_hash_many_guarded": (i, [vp, C.POINTER(NxHashRecord), sz, vp, C.POINTER(u64)]),
         "nx_kawpow_verify_batch": (i, [vp, C.POINTER(NxVerifyRecord), sz, u8p]),
         "nx_ethash_hash": (i, [vp, u8p, u64, C.POINTER(NxResult)]),
         "nx_ethash_hash_batch": (i, [vp, u8p, u64, u64, vp]),

@@ -139,7 +139,10 @@ void destroy(nx_epoch* c)
     delete c;
 }
 
-int create(int epoch, int device, int rank, int world, const uint8_t* light_in, bool deferred, nx_epoch** out)
+// light_later: allocate only; the light cache arrives through nx_epoch_build_light_cache (the rank that runs the
+// serial chain) or nx_epoch_adopt_light_cache (the ranks it is broadcast to).  Implies deferred.
+int create(int epoch, int device, int rank, int world, const uint8_t* light_in, bool deferred, nx_epoch** out,
+           bool light_later = false)
 {
     clear_error();
     if (!out) {
@@ -206,7 +209,9 @@ int create(int epoch, int device, int rank, int world, const uint8_t* light_in, 
     nx_epoch_seed(epoch, seed);
     const char* mode = std::getenv("NX_LIGHT_CACHE");
     const auto t0 = std::chrono::steady_clock::now();
-    if (light_in) {  // caller already ran the serial chain (one host build shared by several devices)
+    if (light_later) {
+        c->light_pending = true;
+    } else if (light_in) {  // caller already ran the serial chain (one host build shared by several devices)
         std::memcpy(c->light_host, light_in, light_bytes);
         NX_TRY(cudaMemcpyAsync(c->light_dev, c->light_host, light_bytes, cudaMemcpyHostToDevice, c->stream));
     } else if (mode && std::strcmp(mode, "gpu") == 0) {
@@ -287,6 +292,71 @@ int nx_epoch_create_deferred(int epoch, int device, int rank, int world, const u
     return create(epoch, device, rank, world, light_cache, true, out);
 }
 
+int nx_epoch_create_shell(int epoch, int device, int rank, int world, nx_epoch** out)
+{
+    return create(epoch, device, rank, world, nullptr, true, out, true);
+}
+
+int nx_epoch_build_light_cache(nx_epoch* c)
+{
+    if (!c) {
+        set_error("null epoch context");
+        return NX_ERR_INVALID;
+    }
+    if (!c->light_pending) {
+        set_error("this context already has its light cache");
+        return NX_ERR_STATE;
+    }
+    // the serial chain touches only light_host: the context stays usable from other threads (IPC set-up) meanwhile
+    uint8_t seed[32];
+    nx_epoch_seed(c->epoch, seed);
+    const auto t0 = std::chrono::steady_clock::now();
+    const char* mode = std::getenv("NX_LIGHT_CACHE");
+    const size_t light_bytes = (size_t)c->light_items * 64;
+    const bool on_gpu = mode && std::strcmp(mode, "gpu") == 0;
+    if (!on_gpu && !host_load_light_cache(c->light_host, c->light_items, c->epoch)) {
+        host_build_light_cache(c->light_host, c->light_items, seed);
+        host_store_light_cache(c->light_host, c->light_items, c->epoch);
+    }
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    if (on_gpu) {
+        const int rc = light_cache_build_gpu(c->light_dev, c->light_items, seed, c->stream);
+        if (rc != NX_OK) return rc;
+        NX_CUDA(cudaMemcpyAsync(c->light_host, c->light_dev, light_bytes, cudaMemcpyDeviceToHost, c->stream));
+    } else {
+        NX_CUDA(cudaMemcpyAsync(c->light_dev, c->light_host, light_bytes, cudaMemcpyHostToDevice, c->stream));
+    }
+    NX_CUDA(cudaStreamSynchronize(c->stream));
+    c->light_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->light_pending = false;
+    return NX_OK;
+}
+
+void* nx_epoch_light_ptr(const nx_epoch* c) { return c ? c->light_dev : nullptr; }
+
+int nx_epoch_adopt_light_cache(nx_epoch* c)
+{
+    if (!c) {
+        set_error("null epoch context");
+        return NX_ERR_INVALID;
+    }
+    if (!c->light_pending) {
+        set_error("this context already has its light cache");
+        return NX_ERR_STATE;
+    }
+    std::lock_guard<std::recursive_mutex> lk(c->mu);
+    NX_CUDA(cudaSetDevice(c->device));
+    const auto t0 = std::chrono::steady_clock::now();
+    // the device buffer was filled by the caller (a broadcast from the rank that ran the chain): mirror it for the
+    // reference-visible light_cache field
+    NX_CUDA(cudaMemcpyAsync(c->light_host, c->light_dev, (size_t)c->light_items * 64, cudaMemcpyDeviceToHost, c->stream));
+    NX_CUDA(cudaStreamSynchronize(c->stream));
+    c->light_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->light_pending = false;
+    return NX_OK;
+}
+
 int nx_epoch_ipc_handle(const nx_epoch* c, uint8_t handle[64])
 {
     if (!c || !handle) {
@@ -302,10 +372,15 @@ int nx_epoch_ipc_handle(const nx_epoch* c, uint8_t handle[64])
 }
 
 // Generate this rank's slice and store it into every rank's DAG buffer in the same kernel.
+// peer_bases == nullptr: the slice goes into the own buffer only (the caller all-gathers afterwards).
 static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries; [rank] may be null */)
 {
     if (!c->deferred) {
         set_error("context was not created with nx_epoch_create_deferred (its slice is already generated)");
+        return NX_ERR_STATE;
+    }
+    if (c->light_pending) {
+        set_error("this context has no light cache yet (nx_epoch_build_light_cache / nx_epoch_adopt_light_cache come first)");
         return NX_ERR_STATE;
     }
     if (c->world > NX_MAX_PEERS) {
@@ -318,7 +393,7 @@ static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries;
     void* outs[NX_MAX_PEERS];
     int n = 0;
     outs[n++] = (char*)c->dag_dev + (size_t)first * 256;  // local copy first
-    for (int r = 0; r < c->world; ++r) {
+    for (int r = 0; peer_bases && r < c->world; ++r) {
         if (r == c->rank) continue;
         if (!peer_bases[r]) {  // e.g. a rank whose context could not be created: never offset a null pointer
             set_error("no DAG buffer given for rank %d", r);
@@ -343,12 +418,11 @@ static int generate_fused(nx_epoch* c, void* const* peer_bases /* world entries;
     return NX_OK;
 }
 
-static int nx_epoch_generate_fused_ipc_body(nx_epoch* c, const uint8_t* handles /* world x 64 bytes, indexed by rank */)
+// Map every other rank's DAG buffer into this process (cudaIpcOpenMemHandle, tens of ms each for a multi-GiB buffer).
+// Needs no light cache, so a multi-process build does it while the one serial chain is still running.
+static int open_ipc_peers(nx_epoch* c, const uint8_t* handles /* world x 64 bytes, indexed by rank */)
 {
-    if (!c || !handles) {
-        set_error("null argument");
-        return NX_ERR_INVALID;
-    }
+    if (!c->ipc_bases.empty()) return NX_OK;  // already open
     NX_CUDA(cudaSetDevice(c->device));
     std::vector<void*> bases((size_t)c->world, nullptr);
     for (int r = 0; r < c->world; ++r) {
@@ -365,7 +439,39 @@ static int nx_epoch_generate_fused_ipc_body(nx_epoch* c, const uint8_t* handles 
         c->ipc_opened.push_back(p);
         bases[(size_t)r] = p;
     }
-    return generate_fused(c, bases.data());
+    c->ipc_bases = bases;
+    return NX_OK;
+}
+
+static int nx_epoch_generate_fused_ipc_body(nx_epoch* c, const uint8_t* handles /* may be null after nx_epoch_open_ipc_peers */)
+{
+    if (!c || (!handles && c->ipc_bases.empty())) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if (c->ipc_bases.empty()) {
+        const int rc = open_ipc_peers(c, handles);
+        if (rc != NX_OK) return rc;
+    }
+    return generate_fused(c, c->ipc_bases.data());
+}
+
+int nx_epoch_open_ipc_peers(nx_epoch* c, const uint8_t* handles)
+{
+    if (!c || !handles) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    return guarded([&] { return open_ipc_peers(c, handles); });
+}
+
+int nx_epoch_generate_slice(nx_epoch* c)
+{
+    if (!c) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    return generate_fused(c, nullptr);  // own buffer only: the exchange is the caller's in-place all-gather
 }
 
 int nx_epoch_generate_fused_peers(nx_epoch* c, void* const* peer_dag_ptrs /* world entries, same process */)
@@ -944,6 +1050,90 @@ static int nx_kawpow_verify_batch_body(const nx_epoch* c, const nx_verify_record
 int nx_epoch_generate_fused_ipc(nx_epoch* c, const uint8_t* handles /* world x 64 bytes, indexed by rank */)
 {
     return guarded([&] { return nx_epoch_generate_fused_ipc_body(c, handles); });
+}
+
+// Test hook (not declared in include/: the tests bind it through ctypes).  compute-sanitizer is not available on every
+// pool, so this runs the per-record kernel K6 on buffers of EXACTLY the bytes it may touch, each between two 4 KiB
+// guard zones filled with a pattern, and reports how many guard bytes the kernel changed (0 = no out-of-bounds
+// store).  Records and programs are laid out as nx_kawpow_hash_many lays them out; out_host receives n x 64 bytes.
+int nx_test_hash_many_guarded(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host,
+                              uint64_t* guard_bytes_changed)
+{
+    return guarded([&]() -> int {
+        nx_epoch* c = const_cast<nx_epoch*>(cc);
+        int rc = check_ctx(c, 0);
+        if (rc != NX_OK) return rc;
+        if (!records || !out_host || !guard_bytes_changed || n == 0 || n > (1u << 20)) {
+            set_error("bad argument");
+            return NX_ERR_INVALID;
+        }
+        std::map<uint64_t, uint32_t> slot_of;
+        std::vector<KawpowRecord> recs(n);
+        for (size_t i = 0; i < n; ++i) {
+            const int bn = records[i].block_number;
+            if (bn < 0 || bn / NX_EPOCH_LENGTH != c->epoch) {
+                set_error("record %zu: block %d is not in this context's epoch %d", i, bn, c->epoch);
+                return NX_ERR_INVALID;
+            }
+            const uint64_t seed = (uint64_t)(bn / NX_PERIOD_LENGTH);
+            auto it = slot_of.find(seed);
+            if (it == slot_of.end()) it = slot_of.emplace(seed, (uint32_t)slot_of.size()).first;
+            std::memcpy(recs[i].header, records[i].header_hash, 32);
+            recs[i].nonce = records[i].nonce;
+            recs[i].program_slot = it->second;
+            recs[i].pad = 0;
+        }
+        std::vector<uint32_t> progs(slot_of.size() * 36 * 4);
+        for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);
+
+        constexpr size_t G = 4096;
+        const size_t sizes[3] = {n * sizeof(KawpowRecord), progs.size() * 4, n * 64};
+        size_t off[3], total = 0;
+        for (int k = 0; k < 3; ++k) {
+            total += G;
+            off[k] = total;
+            total += (sizes[k] + 255) & ~(size_t)255;  // the next guard starts right behind the rounded payload ...
+        }
+        total += G;
+        std::lock_guard<std::recursive_mutex> lk(c->mu);
+        NX_CUDA(cudaSetDevice(c->device));
+        char* buf = nullptr;
+        if (cudaMalloc((void**)&buf, total) != cudaSuccess) {
+            cudaGetLastError();
+            set_error("out of device memory");
+            return NX_ERR_OOM;
+        }
+        std::vector<uint8_t> before(total, 0xA5), after(total);
+        auto done = [&](int code) {
+            cudaFree(buf);
+            return code;
+        };
+        if (cudaMemcpy(buf, before.data(), total, cudaMemcpyHostToDevice) != cudaSuccess) return done(NX_ERR_CUDA);
+        if (cudaMemcpy(buf + off[0], recs.data(), sizes[0], cudaMemcpyHostToDevice) != cudaSuccess) return done(NX_ERR_CUDA);
+        if (cudaMemcpy(buf + off[1], progs.data(), sizes[1], cudaMemcpyHostToDevice) != cudaSuccess) return done(NX_ERR_CUDA);
+        rc = kawpow_interp_launch(c->dag_dev, c->dag_items, reinterpret_cast<const KawpowRecord*>(buf + off[0]), (uint32_t)n,
+                                  buf + off[1], buf + off[2], c->stream);
+        if (rc != NX_OK) return done(rc);
+        if (cudaStreamSynchronize(c->stream) != cudaSuccess || cudaMemcpy(after.data(), buf, total, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            set_error("guarded run failed: %s", cudaGetErrorString(cudaGetLastError()));
+            return done(NX_ERR_CUDA);
+        }
+        std::memcpy(out_host, after.data() + off[2], sizes[2]);
+        // ... so everything outside the three exact payloads - guards AND the rounding slack - must still hold the pattern
+        uint64_t changed = 0;
+        size_t pos = 0;
+        for (int k = 0; k < 3; ++k) {
+            for (; pos < off[k]; ++pos) changed += after[pos] != 0xA5;
+            pos = off[k] + sizes[k];
+            if (k < 2)  // inputs: the kernel never writes them
+                for (size_t q = off[k]; q < off[k] + sizes[k]; ++q)
+                    changed += after[q] != (k == 0 ? reinterpret_cast<const uint8_t*>(recs.data())[q - off[k]]
+                                                   : reinterpret_cast<const uint8_t*>(progs.data())[q - off[k]]);
+        }
+        for (; pos < total; ++pos) changed += after[pos] != 0xA5;
+        *guard_bytes_changed = changed;
+        return done(NX_OK);
+    });
 }
 
 int nx_kawpow_hash_many(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host)

@@ -16,6 +16,8 @@
 #include "nx_internal.hpp"
 #include "nx_keccak.cuh"
 
+#include <cstdlib>
+#include <cstring>
 #include <mutex>
 
 namespace nx
@@ -247,6 +249,133 @@ __global__ void light_cache_kernel(uint64_t* __restrict__ cache, uint32_t n, uin
         }
     }
 }
+// ---- light cache on the GPU, one WARP per permutation (K4w) ----
+// Same serial chain, but Keccak-f[1600] is spread over 25 lanes: lane l = x + 5y holds state word A[x][y].  What counts
+// is the latency of ONE permutation, so the round is laid out for the shortest chain of dependent shuffles:
+//   theta   C[x] by a 2-step butterfly over the five lanes of a column (+1 independent shuffle), D from two shuffles;
+//   rho     a per-lane rotation amount (two funnel shifts after a conditional swap of the halves);
+//   pi+chi  ONE step: the three operands b[x], b[x+1], b[x+2] of chi are fetched straight from the pre-pi lanes
+//           (source lane = pi^-1 of the operand's position), so pi costs no shuffle of its own;
+//   iota    lane 0.
+// Four dependent 64-bit shuffles per round.  The item index of the second phase (first word of the OLD item i) is
+// prefetched 32 items at a time, and cache[v] of item i+1 is loaded before the permutation of item i starts (the only
+// hazard, v == i, is the case the chain defines as x = 0 anyway).  Bit-identical to the host chain (tests/test_gpu_dag.py).
+struct WarpKeccak
+{
+    uint32_t rot;                 // rho offset of this lane's word
+    int up5, up10, up20;          // lanes of the same column: y+1, y+2, y+4
+    int xm1, xp1;                 // same row, x-1 and x+1
+    int src0, src1, src2;         // pre-pi lanes of b[x][y], b[x+1][y], b[x+2][y]
+};
+
+__device__ __forceinline__ uint64_t shfl64(uint64_t v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
+__device__ __forceinline__ uint64_t rol64_var(uint64_t v, uint32_t n)
+{
+    uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+    if (n & 32u) {
+        const uint32_t t = lo;
+        lo = hi;
+        hi = t;
+    }
+    const uint32_t s = n & 31u;
+    const uint32_t nhi = __funnelshift_l(lo, hi, s), nlo = __funnelshift_l(hi, lo, s);
+    return ((uint64_t)nhi << 32) | nlo;
+}
+
+__device__ __forceinline__ uint64_t warp_keccakf1600(uint64_t a, const WarpKeccak& k, uint32_t lane)
+{
+#pragma unroll 1
+    for (int r = 0; r < 24; ++r) {
+        const uint64_t far = shfl64(a, k.up20);
+        const uint64_t t = a ^ shfl64(a, k.up5);
+        const uint64_t c = t ^ shfl64(t, k.up10) ^ far;
+        const uint64_t cp = shfl64(c, k.xp1), cm = shfl64(c, k.xm1);
+        a ^= cm ^ ((cp << 1) | (cp >> 63));
+        const uint64_t b = rol64_var(a, k.rot);
+        const uint64_t b0 = shfl64(b, k.src0), b1 = shfl64(b, k.src1), b2 = shfl64(b, k.src2);
+        a = b0 ^ (~b1 & b2);
+        if (lane == 0) a ^= KECCAK_RC_DEV[r];
+    }
+    return a;
+}
+
+__global__ void __launch_bounds__(32) light_cache_warp_kernel(uint64_t* __restrict__ cache, uint32_t n, uint64_t s0,
+                                                              uint64_t s1, uint64_t s2, uint64_t s3)
+{
+    if (blockIdx.x != 0) return;
+    const uint32_t lane = threadIdx.x;
+    WarpKeccak k;
+    {
+        const uint32_t RHO[25] = {0, 1, 62, 28, 27, 36, 44, 6, 55, 20, 3, 10, 43, 25, 39, 41, 45, 15, 21, 8, 18, 2, 61, 56, 14};
+        const uint32_t l = lane < 25u ? lane : 0u;  // lanes 25..31 mirror lane 0's wiring and carry zeros
+        const uint32_t x = l % 5u, y = l / 5u;
+        k.rot = RHO[l];
+        k.up5 = (int)((l + 5u) % 25u);
+        k.up10 = (int)((l + 10u) % 25u);
+        k.up20 = (int)((l + 20u) % 25u);
+        k.xm1 = (int)((x + 4u) % 5u + 5u * y);
+        k.xp1 = (int)((x + 1u) % 5u + 5u * y);
+        // pi: the word at (x', y') moves to (y', 2x' + 3y'); so position (X, Y) is fed from x' = (X + 3Y) % 5, y' = X
+        auto pre_pi = [](uint32_t X, uint32_t Y) { return (int)((X + 3u * Y) % 5u + 5u * X); };
+        k.src0 = pre_pi(x, y);
+        k.src1 = pre_pi((x + 1u) % 5u, y);
+        k.src2 = pre_pi((x + 2u) % 5u, y);
+    }
+    const uint64_t PAD64 = 0x8000000000000001ULL;  // keccak512 of 64 bytes: 0x01 and 0x80 both land in word 8
+    // item 0 = keccak512(seed)
+    uint64_t a = lane == 0 ? s0 : lane == 1 ? s1 : lane == 2 ? s2 : lane == 3 ? s3 : lane == 4 ? 0x01ULL
+                                                                                 : lane == 8 ? 0x8000000000000000ULL : 0ULL;
+    a = warp_keccakf1600(a, k, lane);
+    if (lane < 8) cache[lane] = a;
+    for (uint32_t i = 1; i < n; ++i) {
+        a = lane < 8 ? a : lane == 8 ? PAD64 : 0ULL;
+        a = warp_keccakf1600(a, k, lane);
+        if (lane < 8) cache[8 * (size_t)i + lane] = a;
+    }
+    __threadfence();
+    for (int q = 0; q < 3; ++q) {
+        // lanes 0..7 of `a` hold item (i-1) mod n; before i = 0 that is the last item of the previous pass (still in `a`)
+        uint32_t idx_words = 0, idx_next = 0;
+        uint64_t operand = 0;  // cache[v] of the item about to be processed, lanes 0..7
+        uint32_t v_cur = 0;
+        for (uint32_t i = 0; i < n; ++i) {
+            const uint32_t j = i & 31u;
+            if (j == 0) {
+                // old first words of items i..i+31 (none of them rewritten yet in this pass)
+                if (i == 0) {
+                    const uint32_t it = i + lane;
+                    idx_words = it < n ? (uint32_t)__ldcg(cache + 8 * (size_t)it) : 0u;
+                    v_cur = __shfl_sync(0xffffffffu, idx_words, 0) % n;
+                    operand = lane < 8 ? __ldcg(cache + 8 * (size_t)v_cur + lane) : 0ULL;
+                } else {
+                    idx_words = idx_next;
+                }
+            }
+            if (j == 8) {  // next group's index words, 24 items ahead of their first use
+                const uint32_t it = i - 8u + 32u + lane;
+                idx_next = it < n ? (uint32_t)__ldcg(cache + 8 * (size_t)it) : 0u;
+            }
+            // v of the NEXT item and its operand, issued before this item's permutation
+            const uint32_t w_next = i;  // item i is (i+1)-1
+            uint32_t v_next = 0;
+            uint64_t operand_next = 0;
+            const bool has_next = i + 1u < n;
+            if (has_next) {
+                const uint32_t word = j == 31u ? __shfl_sync(0xffffffffu, idx_next, 0) : __shfl_sync(0xffffffffu, idx_words, (int)(j + 1u));
+                v_next = word % n;
+                if (v_next != w_next && lane < 8) operand_next = __ldcg(cache + 8 * (size_t)v_next + lane);
+            }
+            const uint32_t w = i == 0 ? n - 1u : i - 1u;
+            uint64_t x = lane < 8 ? (v_cur == w ? 0ULL : (a ^ operand)) : lane == 8 ? PAD64 : 0ULL;
+            a = warp_keccakf1600(x, k, lane);
+            if (lane < 8) __stcg(cache + 8 * (size_t)i + lane, a);
+            v_cur = v_next;
+            operand = operand_next;
+        }
+    }
+}
+
 // ---- classic Ethash hash (K7) ----
 // Replaces hash_seed / hash_kernel / hash_final (reference ethash.cpp:257-303) applied to a batch of
 // nonces.  The DAG is addressed as 128-byte items here (index_limit = full_dataset_num_items, :279).
@@ -417,10 +546,45 @@ extern "C" int nx_dag_checksum_noalloc(const void* data_device, size_t n_bytes, 
                   "(make the device that owns it current first)", dev);
         return NX_ERR_INVALID;
     }
+    {
+        // The attributes above describe the base pointer only.  Ask the driver for the extent of the allocation
+        // around it (a query, nothing is allocated) and refuse a range that runs past its end: the kernel would
+        // otherwise fault and leave the context with a sticky error.  Memory the driver cannot describe this way
+        // (some mapped ranges) is let through unchecked.
+        typedef int (*get_range_fn)(unsigned long long*, size_t*, unsigned long long);
+        static get_range_fn get_range = [] {
+            void* fn = nullptr;
+            cudaDriverEntryPointQueryResult st;
+            if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &st) != cudaSuccess ||
+                st != cudaDriverEntryPointSuccess)
+                fn = nullptr;
+            cudaGetLastError();
+            return reinterpret_cast<get_range_fn>(fn);
+        }();
+        unsigned long long base = 0;
+        size_t size = 0;
+        if (get_range && get_range(&base, &size, (unsigned long long)(uintptr_t)data_device) == 0 && size != 0) {
+            const unsigned long long p = (unsigned long long)(uintptr_t)data_device;
+            if (p < base || n_bytes > size || p - base > size - n_bytes) {
+                set_error("nx_dag_checksum_noalloc: %zu bytes from this pointer run past the end of its allocation "
+                          "(%zu bytes, the pointer sits at offset %llu)", n_bytes, size, p - base);
+                return NX_ERR_INVALID;
+            }
+        }
+    }
     uint64_t* scratch = nullptr;
     {
-        // One-time set-up per device, with that device current: resolve the symbol to its device address.
+        // One-time set-up per device, with that device current: resolve the symbol to its device address.  The
+        // address dies with the context (cudaDeviceReset): a cached one that the driver no longer knows as memory
+        // of this device is looked up again.
         std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (g_noalloc_ptr[dev]) {
+            cudaPointerAttributes sa;
+            if (cudaPointerGetAttributes(&sa, g_noalloc_ptr[dev]) != cudaSuccess || sa.type != cudaMemoryTypeDevice ||
+                sa.device != dev)
+                g_noalloc_ptr[dev] = nullptr;
+            cudaGetLastError();
+        }
         if (!g_noalloc_ptr[dev]) {
             void* p = nullptr;
             const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
@@ -509,7 +673,12 @@ int light_cache_build_gpu(void* light_dev, int light_items, const uint8_t seed[3
 {
     uint64_t w[4];
     memcpy(w, seed, 32);
-    light_cache_kernel<<<1, 32, 0, s>>>(static_cast<uint64_t*>(light_dev), (uint32_t)light_items, w[0], w[1], w[2], w[3]);
+    // NX_LIGHT_CACHE_KERNEL=thread selects the first version (one thread does the whole permutation)
+    const char* which = std::getenv("NX_LIGHT_CACHE_KERNEL");
+    if (which && std::strcmp(which, "thread") == 0)
+        light_cache_kernel<<<1, 32, 0, s>>>(static_cast<uint64_t*>(light_dev), (uint32_t)light_items, w[0], w[1], w[2], w[3]);
+    else
+        light_cache_warp_kernel<<<1, 32, 0, s>>>(static_cast<uint64_t*>(light_dev), (uint32_t)light_items, w[0], w[1], w[2], w[3]);
     NX_CUDA(cudaGetLastError());
     return NX_OK;
 }

@@ -143,7 +143,9 @@ struct nx_epoch
     void* batch_out_dev = nullptr;
     size_t batch_out_bytes = 0;
     bool deferred = false;     // slice not generated yet (waiting for nx_epoch_generate_fused*)
+    bool light_pending = false;  // created by nx_epoch_create_shell: the light cache has not arrived yet
     std::vector<void*> ipc_opened;  // peer DAG buffers opened with cudaIpcOpenMemHandle
+    std::vector<void*> ipc_bases;   // the same, indexed by rank (own entry null), once nx_epoch_open_ipc_peers has run
     void* many_dev = nullptr;  // records + packed programs of nx_kawpow_hash_many
     size_t many_bytes = 0;
     // bookkeeping for enqueue/sync

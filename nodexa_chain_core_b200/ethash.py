@@ -56,9 +56,12 @@ class EpochContext:
     """
 
     def __init__(self, epoch_number: int, device: int = 0, rank: int = 0, world: int = 1, deferred: bool = False,
-                 light_cache: bytes = None):
+                 light_cache: bytes = None, shell: bool = False):
         h = C.c_void_p()
-        if deferred:
+        if shell:
+            # allocations only: the light cache comes from build_light_cache() (one rank) or adopt_light_cache() (the others)
+            check(lib.nx_epoch_create_shell(epoch_number, device, rank, world, C.byref(h)))
+        elif deferred:
             # light_cache: the epoch's light cache if the caller already has it (one serial chain for several contexts)
             lc = C.cast(C.c_char_p(light_cache), C.c_void_p) if light_cache is not None else None
             check(lib.nx_epoch_create_deferred(epoch_number, device, rank, world, lc, C.byref(h)))
@@ -127,10 +130,32 @@ class EpochContext:
         check(lib.nx_epoch_ipc_handle(self._h, o))
         return bytes(o)
 
-    def generate_fused_ipc(self, handles_by_rank) -> None:
-        """handles_by_rank: list of `world` 64-byte blobs from every rank's ipc_handle() (own entry ignored)."""
-        blob = b"".join(handles_by_rank)
-        check(lib.nx_epoch_generate_fused_ipc(self._h, inb(blob)))
+    def generate_fused_ipc(self, handles_by_rank=None) -> None:
+        """handles_by_rank: list of `world` 64-byte blobs from every rank's ipc_handle() (own entry ignored);
+        None once open_ipc_peers() has mapped them."""
+        if handles_by_rank is None:
+            check(lib.nx_epoch_generate_fused_ipc(self._h, None))
+        else:
+            check(lib.nx_epoch_generate_fused_ipc(self._h, inb(b"".join(handles_by_rank))))
+
+    def generate_slice(self) -> None:
+        """Shell / deferred contexts on the NCCL route: this rank's slice into its own buffer; all-gather + finalize follow."""
+        check(lib.nx_epoch_generate_slice(self._h))
+
+    def open_ipc_peers(self, handles_by_rank) -> None:
+        check(lib.nx_epoch_open_ipc_peers(self._h, inb(b"".join(handles_by_rank))))
+
+    def build_light_cache(self) -> None:
+        """Shell contexts: run the serial chain here (the one rank of a job that does)."""
+        check(lib.nx_epoch_build_light_cache(self._h))
+
+    def adopt_light_cache(self) -> None:
+        """Shell contexts: light_tensor() has been filled by a broadcast from the rank that ran the chain."""
+        check(lib.nx_epoch_adopt_light_cache(self._h))
+
+    def light_tensor(self):
+        """The light cache on the device as a torch uint8 CUDA tensor aliasing the library's buffer (for NCCL)."""
+        return self._alias_tensor(lib.nx_epoch_light_ptr(self._h), self.light_cache_num_items * 64)
 
     def generate_fused_peers(self, dag_ptrs_by_rank) -> None:
         """dag_ptrs_by_rank: `world` device pointers (dag_ptr of every rank's context in THIS process; own entry ignored)."""
@@ -143,14 +168,16 @@ class EpochContext:
 
     def dag_tensor(self):
         """The padded DAG as a torch uint8 CUDA tensor aliasing the library's buffer (for NCCL)."""
+        return self._alias_tensor(self.dag_ptr, self.dag_padded_bytes)
+
+    def _alias_tensor(self, ptr: int, nbytes: int):
         import torch
 
         class _Arr:
             pass
 
         a = _Arr()
-        a.__cuda_array_interface__ = {"shape": (self.dag_padded_bytes,), "typestr": "|u1",
-                                      "data": (self.dag_ptr, False), "version": 2}
+        a.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
         a._keepalive = self
         return torch.as_tensor(a, device=f"cuda:{self.device}")
 

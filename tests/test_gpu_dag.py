@@ -98,14 +98,22 @@ def test_sharded_build_slices_equal_full_dag(nx, ctx_of, world):
             c.close()
 
 
-def test_light_cache_gpu_kernel_matches_host(nx, monkeypatch):
-    """K4 (serial chain on the device) produces the same light cache and DAG as the host build."""
+@pytest.mark.parametrize("kernel,epoch", [("warp", 0), ("thread", 0), ("warp", 448)])
+def test_light_cache_gpu_kernels_match_the_reference_digest(nx, monkeypatch, kernel, epoch):
+    """K4 (the serial chain on the device; "warp" = one Keccak-f[1600] spread over 25 lanes, "thread" = the first
+    version) produces the light cache the reference's build_light_cache produces (ethash.cpp:101-129) - the whole
+    cache by sha256 - and with it the same L1 cache / DAG.  Epoch 448 (72 MiB, 4.7 M permutations) is the bench's."""
+    import time
     monkeypatch.setenv("NX_LIGHT_CACHE", "gpu")
-    c = nx.EpochContext(0, 0)
+    monkeypatch.setenv("NX_LIGHT_CACHE_KERNEL", kernel)
+    t0 = time.perf_counter()
+    c = nx.EpochContext(epoch, 0)
     try:
+        light_ms, _ = c.build_times_ms()
+        print(f"K4 {kernel} epoch {epoch}: light cache {light_ms:.0f} ms on the device (whole create {time.perf_counter() - t0:.2f} s)")
         e = golden("epochs.json")
-        assert hashlib.sha256(c.light_cache).hexdigest() == e["light_cache_sha256_epoch0"]
-        assert hashlib.sha256(struct.pack("<4096I", *c.l1_cache)).hexdigest() == e["l1_sha256_epoch0"]
+        assert hashlib.sha256(c.light_cache).hexdigest() == e[f"light_cache_sha256_epoch{epoch}"]
+        assert hashlib.sha256(struct.pack("<4096I", *c.l1_cache)).hexdigest() == e[f"l1_sha256_epoch{epoch}"]
     finally:
         c.close()
 

@@ -166,3 +166,36 @@ def test_external_miner_rpc_surface(nx, ctx_of, oracle):
     # the right nonce with somebody else's mix passes this gate (GetHashFull ignores the claim) and fails the next one
     accepted, forged = node.pprpcsb_check(ctx0, tmpl, "ab" * 32, "%x" % sr.nonce)
     assert accepted and node.check_block_headers(ctx0, [forged])[0] in (node.HEADER_INVALID_MIX, node.HEADER_HIGH_HASH)
+
+
+@pytest.mark.parametrize("periods", [1, 2, 33])
+def test_per_record_kernel_stays_inside_its_buffers(nx, ctx_of, periods):
+    """compute-sanitizer is closed on this pool, so the per-record kernel (K6: one CTA = 8 records, dead slots of the
+    last CTA re-read record n-1) is run on buffers of exactly the bytes it may touch, each between guard zones: no guard
+    byte and no input byte may change, for record counts around the CTA size, and the hashes must equal the regular
+    entry point's (nx_kawpow_hash_many, and through it nx_kawpow_verify_batch / nx_check_block_headers)."""
+    import ctypes as C
+
+    from nodexa_chain_core_b200._lib import NxHashRecord, check, outb
+    ctx = ctx_of(0)
+    rnd = random.Random(800 + periods)
+    heights = [3 * rnd.randrange(2500) for _ in range(periods)]
+    for n in (1, 7, 8, 9, 17, 64, 65):
+        recs = [(heights[i % periods] + rnd.randrange(3), rnd.randbytes(32), rnd.getrandbits(64)) for i in range(n)]
+        arr = (NxHashRecord * n)()
+        for i, (bn, hd, nonce) in enumerate(recs):
+            arr[i].block_number, arr[i].nonce = bn, nonce
+            C.memmove(arr[i].header_hash, hd, 32)
+        out = outb(64 * n)
+        changed = C.c_uint64(12345)
+        check(nx.lib.nx_test_hash_many_guarded(ctx._h, arr, n, out, C.byref(changed)))
+        assert changed.value == 0, (n, periods, changed.value)
+        want = progpow.hash_many(ctx, recs)
+        assert bytes(out) == b"".join(r.final_hash + r.mix_hash for r in want), (n, periods)
+        # the batch-verify entry built on the same kernel agrees record by record
+        vrecs = [(bn, hd, w.mix_hash, nonce, w.final_hash) for (bn, hd, nonce), w in zip(recs, want)]
+        assert progpow.verify_batch(ctx, vrecs) == [True] * n
+    # one record checked against the KAT so that "equal to hash_many" is not a closed loop
+    k = golden("kawpow_kats.json")["hash_cases"][0]
+    r = progpow.hash_many(ctx, [(k["height"], bytes.fromhex(k["header"]), k["nonce"])])[0]
+    assert r.final_hash.hex() == k["final"]

@@ -80,3 +80,9 @@ def test_noalloc_checksum_rejects_what_it_cannot_serve(nx, ctx_of):
     assert _noalloc(nx, C.addressof(host), 32)[0] < 0   # host memory is not accepted
     rc = nx.lib.nx_dag_checksum_noalloc(C.c_void_p(ctx.dag_ptr), 8, None, None)
     assert rc == -1                                      # null output
+    # a range that leaves the allocation is refused up front instead of faulting inside the kernel
+    assert _noalloc(nx, ctx.dag_ptr, ctx.dag_padded_bytes + (64 << 20))[0] == -1
+    assert "past the end" in nx.lib.nx_last_error().decode()
+    assert _noalloc(nx, ctx.dag_ptr + (8 << 20), ctx.dag_padded_bytes)[0] == -1
+    rc, got = _noalloc(nx, ctx.dag_ptr, ctx.dag_bytes)  # and the device is still healthy
+    assert rc == 0 and got == golden("dag_digest.json")["0"]["weighted_sum"]
