@@ -384,6 +384,8 @@ __global__ void __launch_bounds__(32) light_cache_warp_kernel(uint64_t* __restri
 // 16-byte load per lane = one contiguous 128-byte item per group (4 items per warp-wide load).
 // Algorithmic bytes: 64 x 128 B = 8 192 B of DAG per hash.
 constexpr int ETHASH_THREADS = 128;
+// Q = nonces of a group walked at the same time (4 or 8): Q independent 128-byte reads in flight per group.
+template <int Q>
 __global__ void __launch_bounds__(ETHASH_THREADS)
 ethash_hash_kernel(const uint4* __restrict__ dag, FastMod fm, uint64_t h0, uint64_t h1, uint64_t h2, uint64_t h3,
                    uint64_t start_nonce, uint64_t count, uint4* __restrict__ out)
@@ -409,15 +411,14 @@ ethash_hash_kernel(const uint4* __restrict__ dag, FastMod fm, uint64_t h0, uint6
 #pragma unroll
     for (int i = 0; i < 8; ++i) mh[i] = 0;
 
-    // Four nonces of the group are walked at the same time (four independent 128-byte reads in flight per group).
 #pragma unroll 1
-    for (uint32_t p0 = 0; p0 < 8; p0 += 4) {
+    for (uint32_t p0 = 0; p0 < 8; p0 += Q) {
         // the 32-word mix of a nonce starts as its seed twice over: lane s takes words 4s..4s+3,
         // i.e. seed words (4s+c) mod 16 = 4*(s&3)+c
-        uint32_t m[4][4];
-        uint32_t seed0[4];
+        uint32_t m[Q][4];
+        uint32_t seed0[Q];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < Q; ++q) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) m[q][c] = 0;
 #pragma unroll
@@ -432,14 +433,14 @@ ethash_hash_kernel(const uint4* __restrict__ dag, FastMod fm, uint64_t h0, uint6
 #pragma unroll
             for (uint32_t ii = 0; ii < 32; ++ii) {
                 // mix word ii lives in lane ii/4, component ii%4
-                uint4 v[4];
+                uint4 v[Q];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
+                for (int q = 0; q < Q; ++q) {
                     const uint32_t t = fnv1((i + ii) ^ seed0[q], __shfl_sync(0xffffffffu, m[q][ii & 3], ii >> 2, 8));
                     v[q] = __ldg(dag + (size_t)fast_mod(t, fm) * 8 + sub);
                 }
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
+                for (int q = 0; q < Q; ++q) {
                     m[q][0] = fnv1(m[q][0], v[q].x);
                     m[q][1] = fnv1(m[q][1], v[q].y);
                     m[q][2] = fnv1(m[q][2], v[q].z);
@@ -449,7 +450,7 @@ ethash_hash_kernel(const uint4* __restrict__ dag, FastMod fm, uint64_t h0, uint6
         }
         // lane s holds words 4s..4s+3 -> compressed word s of each mix hash; hand all 8 words to the owner lane
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < Q; ++q) {
             const uint32_t h = fnv1(fnv1(fnv1(m[q][0], m[q][1]), m[q][2]), m[q][3]);
 #pragma unroll
             for (int w = 0; w < 8; ++w) {
@@ -663,8 +664,16 @@ int ethash_hash_batch(const void* dag_dev, uint32_t num_items_128, const uint8_t
     FastMod fm;
     fm.d = num_items_128;
     fm.m = (uint32_t)((1ull << 32) / fm.d);
-    ethash_hash_kernel<<<(unsigned)blocks, ETHASH_THREADS, 0, s>>>(static_cast<const uint4*>(dag_dev), fm, h[0], h[1], h[2],
-                                                                  h[3], start_nonce, count, static_cast<uint4*>(out_dev));
+    static const int q = [] {  // NX_ETHASH_INFLIGHT=4|8 (measurement knob)
+        const char* e = std::getenv("NX_ETHASH_INFLIGHT");
+        return e && std::atoi(e) == 8 ? 8 : 4;
+    }();
+    if (q == 8)
+        ethash_hash_kernel<8><<<(unsigned)blocks, ETHASH_THREADS, 0, s>>>(static_cast<const uint4*>(dag_dev), fm, h[0], h[1],
+                                                                         h[2], h[3], start_nonce, count, static_cast<uint4*>(out_dev));
+    else
+        ethash_hash_kernel<4><<<(unsigned)blocks, ETHASH_THREADS, 0, s>>>(static_cast<const uint4*>(dag_dev), fm, h[0], h[1],
+                                                                         h[2], h[3], start_nonce, count, static_cast<uint4*>(out_dev));
     NX_CUDA(cudaGetLastError());
     return NX_OK;
 }

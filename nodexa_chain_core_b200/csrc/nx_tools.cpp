@@ -102,3 +102,12 @@ int nx_host_light_cache_cached(int epoch, uint8_t* out)
     return 0;
 }
 }
+
+extern "C" {
+// The launch shape the KawPow kernel gets for `count` nonces on a device with `sms` multiprocessors (CPU tests).
+void nx_kawpow_launch_shape(uint64_t count, int threads, int sms, int minblocks, int persist, uint32_t* per_hw,
+                            uint32_t* n_units, uint32_t* grid)
+{
+    kawpow_launch_shape(count, threads, sms, minblocks, persist != 0, per_hw, n_units, grid);
+}
+}

@@ -185,3 +185,35 @@ def test_light_cache_file_cache(tmp_path, monkeypatch):
     assert lib.nx_host_light_cache_cached(0, buf3) == 1
     path.write_bytes(path.read_bytes()[:1000])                      # truncated file
     assert lib.nx_host_light_cache_cached(0, buf3) == 0 and hashlib.sha256(buf3.raw).hexdigest() == want
+
+
+def test_kawpow_launch_shape_covers_every_nonce(nx):
+    """nx_kawpow_rt.cpp kawpow_launch_shape: a call is cut into units of 2 x per_hw nonces (one per warp at a time).  Whatever
+    the count, the units must cover it exactly once, per_hw stays in 1..16, the persistent grid never exceeds the resident
+    CTAs, and a 65 536-nonce call (the reference's nInnerLoopCount, src/rpc/mining.cpp:119) is spread over the whole GPU."""
+    import ctypes as C
+    import random
+    f = nx.lib.nx_kawpow_launch_shape
+    f.argtypes = [C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    f.restype = None
+
+    def shape(count, threads=1024, sms=148, minblocks=1, persist=1):
+        k, u, g = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        f(count, threads, sms, minblocks, persist, C.byref(k), C.byref(u), C.byref(g))
+        return k.value, u.value, g.value
+
+    rnd = random.Random(5)
+    counts = [1, 2, 31, 32, 33, 9472, 9473, 65536, 151552, 151553, 1 << 20, 1 << 24, 1 << 32] + [rnd.randrange(1, 1 << 27) for _ in range(200)]
+    for threads, sms, mb in ((1024, 148, 1), (512, 148, 2), (256, 132, 4), (1024, 1, 1)):
+        wpc = threads // 32
+        for count in counts:
+            k, units, grid = shape(count, threads, sms, mb)
+            assert 1 <= k <= 16
+            assert (units - 1) * 2 * k < count <= units * 2 * k          # covered, and no unit is wholly past the end
+            assert 1 <= grid <= sms * mb and grid * wpc >= min(units, sms * mb * wpc - wpc + 1)
+            if count >= 32 * sms * mb * wpc:
+                assert k == 16                                            # large calls: the full 16-nonce walk
+            _, u0, g0 = shape(count, threads, sms, mb, persist=0)
+            assert g0 == -(-u0 // wpc)                                    # non-persistent: one unit per warp
+    assert shape(65536) == (7, 4682, 147)
+    assert shape(1 << 24) == (16, 1 << 19, 148)

@@ -129,15 +129,16 @@ __global__ void __launch_bounds__(256) gather_kernel(const uint4* __restrict__ t
 }
 
 // ------------------------------------------------------------------------------------------------ dram
-// A half-warp reads one random 256-byte item (16 x 16 B) per step, INFLIGHT independent items at a time.
-template <int INFLIGHT>
+// A group of LANES threads reads one random item of LANES x 16 bytes per step (16 lanes = KawPow's 256-byte DAG item,
+// 8 lanes = classic Ethash's 128-byte item), INFLIGHT independent items at a time.
+template <int INFLIGHT, int LANES>
 __global__ void __launch_bounds__(256) dram_kernel(const uint4* __restrict__ buf, u32 items, u32* out, int iters, u32 seed)
 {
     const u32 gid = blockIdx.x * blockDim.x + threadIdx.x;
-    const u32 lane = threadIdx.x & 15u;
+    const u32 lane = threadIdx.x & (LANES - 1);
     u32 s[INFLIGHT];
 #pragma unroll
-    for (int j = 0; j < INFLIGHT; ++j) s[j] = (seed + (gid >> 4) * 2654435761u + j * 0x85ebca6bu) | 1u;
+    for (int j = 0; j < INFLIGHT; ++j) s[j] = (seed + (gid / LANES) * 2654435761u + j * 0x85ebca6bu) | 1u;
     u32 acc = 0;
 #pragma unroll 1
     for (int it = 0; it < iters; ++it) {
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(256) dram_kernel(const uint4* __restrict__ buf
 #pragma unroll
         for (int j = 0; j < INFLIGHT; ++j) {
             const u32 idx = (u32)(((u64)xorshift(s[j]) * items) >> 32);
-            const uint4* p = buf + (size_t)idx * 16 + lane;
+            const uint4* p = buf + (size_t)idx * LANES + lane;
             asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                          : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w)
                          : "l"(p));
@@ -271,16 +272,27 @@ int main(int argc, char** argv)
         fill_kernel<<<sms * 8, 256>>>(buf, (size_t)items * 16);
         const int iters = 1024;
         const int blocks = sms * 8;
-        printf(", \"dram\": {\"buffer_bytes\": %zu, \"item_bytes\": 256", (size_t)items * 256);
-        for (int inflight : {1, 2, 4, 8}) {
-            float ms = time_ms([&] {
-                if (inflight == 1) dram_kernel<1><<<blocks, 256>>>(buf, items, out, iters * 8, 5u);
-                if (inflight == 2) dram_kernel<2><<<blocks, 256>>>(buf, items, out, iters * 4, 5u);
-                if (inflight == 4) dram_kernel<4><<<blocks, 256>>>(buf, items, out, iters * 2, 5u);
-                if (inflight == 8) dram_kernel<8><<<blocks, 256>>>(buf, items, out, iters, 5u);
-            });
-            const double bytes = (double)blocks * 256 / 16 * (double)iters * 8 * 256;
-            printf(", \"inflight_%d\": {\"gb_per_s\": %.1f, \"ms\": %.3f}", inflight, bytes / (ms * 1e-3) / 1e9, ms);
+        printf(", \"dram\": {\"buffer_bytes\": %zu", (size_t)items * 256);
+        for (int lanes : {16, 8}) {
+            printf(", \"item_%d_bytes\": {\"threads_per_sm\": 2048", lanes * 16);
+            for (int inflight : {1, 2, 4, 8}) {
+                float ms = time_ms([&] {
+                    if (lanes == 16) {
+                        if (inflight == 1) dram_kernel<1, 16><<<blocks, 256>>>(buf, items, out, iters * 8, 5u);
+                        if (inflight == 2) dram_kernel<2, 16><<<blocks, 256>>>(buf, items, out, iters * 4, 5u);
+                        if (inflight == 4) dram_kernel<4, 16><<<blocks, 256>>>(buf, items, out, iters * 2, 5u);
+                        if (inflight == 8) dram_kernel<8, 16><<<blocks, 256>>>(buf, items, out, iters, 5u);
+                    } else {
+                        if (inflight == 1) dram_kernel<1, 8><<<blocks, 256>>>(buf, items * 2, out, iters * 8, 5u);
+                        if (inflight == 2) dram_kernel<2, 8><<<blocks, 256>>>(buf, items * 2, out, iters * 4, 5u);
+                        if (inflight == 4) dram_kernel<4, 8><<<blocks, 256>>>(buf, items * 2, out, iters * 2, 5u);
+                        if (inflight == 8) dram_kernel<8, 8><<<blocks, 256>>>(buf, items * 2, out, iters, 5u);
+                    }
+                });
+                const double bytes = (double)blocks * 256 / lanes * (double)iters * 8 * lanes * 16;
+                printf(", \"inflight_%d\": {\"gb_per_s\": %.1f, \"ms\": %.3f}", inflight, bytes / (ms * 1e-3) / 1e9, ms);
+            }
+            printf("}");
         }
         printf("}");
         CK(cudaFree(buf));
