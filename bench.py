@@ -319,6 +319,8 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+        os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: the container's hostname need not resolve
+        cpu_group = dist.new_group(backend="gloo")  # host-side waits that must not keep a spinning NCCL kernel on the GPU
 
     epoch, height = args.epoch, args.epoch * 7500
 
@@ -486,11 +488,15 @@ def main():
             assert plumbing["verified"], "a found nonce failed verification"
 
     paths = None
+    if dist is not None:
+        torch.cuda.synchronize()
     if rank == 0 and not args.no_paths and not measurement_only:
         try:
             paths = secondary_paths(nx, ctx, epoch, height, list(range(world)), measured_peak_gbs()[0])
         except Exception as e:  # noqa: BLE001 - an extra must never sink the bench line
             paths = {"error": repr(e)[:300]}
+    if dist is not None:
+        dist.barrier(group=cpu_group)  # the other ranks wait here on the host while rank 0's miner uses every GPU
 
     # ---- max over ranks ----
     def max_over_ranks(ph):

@@ -341,11 +341,13 @@ static int nx_miner_search_body(nx_miner* m, int block_number, const uint8_t hea
         long done_here = 0;
         for (;;) {
             uint64_t k;
+            bool reissued = false;
             {
                 std::lock_guard<std::mutex> lk(retry_mu);
                 if (!retry.empty()) {
                     k = retry.back();
                     retry.pop_back();
+                    reissued = true;
                 } else {
                     k = next_batch.fetch_add(1, std::memory_order_relaxed);
                 }
@@ -354,7 +356,13 @@ static int nx_miner_search_body(nx_miner* m, int block_number, const uint8_t hea
             const uint64_t off = k * B;
             // Windows are handed out in ascending order, so once a hit exists every window starting above it can
             // be dropped; windows below it that are still running on other devices finish and may lower it.
-            if (off >= best_offset.load(std::memory_order_relaxed)) continue;
+            // A fresh window above the hit ends this worker (every later one lies higher still: with an "unlimited"
+            // iteration count there are 2^40 and more of them, which must not be walked one by one); a re-issued
+            // window above the hit is just dropped, since lower ones may still wait in the retry list.
+            if (off >= best_offset.load(std::memory_order_relaxed)) {
+                if (reissued) continue;
+                break;
+            }
             if (cancel && *cancel) break;
             const uint64_t count = iterations - off < B ? iterations - off : B;
             nx_search_result r;

@@ -19,6 +19,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--epoch", type=int, default=0)
     ap.add_argument("--fused", action="store_true", help="DAG exchange inside the generating kernel (peer stores via CUDA IPC) instead of NCCL")
+    ap.add_argument("--shell", action="store_true", help="one light-cache chain for the job: rank 0 builds it, NCCL broadcasts it "
+                    "(nx_epoch_create_shell / build_light_cache / adopt_light_cache), then --fused or the NCCL all-gather")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -31,14 +33,35 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     dev = f"cuda:{local}"
 
-    ctx = nx.EpochContext(a.epoch, local, rank=rank, world=world, deferred=a.fused)
+    if a.shell:
+        ctx = nx.EpochContext(a.epoch, local, rank=rank, world=world, shell=True)
+        handles = None
+        if a.fused:
+            handles = [None] * world
+            dist.all_gather_object(handles, ctx.ipc_handle())
+            ctx.open_ipc_peers(handles)
+        if rank == 0:
+            ctx.build_light_cache()
+        dist.broadcast(ctx.light_tensor(), src=0)
+        torch.cuda.synchronize()
+        if rank != 0:
+            ctx.adopt_light_cache()
+        gold_e = json.load(open(os.path.join(ROOT, "tests", "golden", "epochs.json")))
+        assert hashlib.sha256(ctx.light_cache).hexdigest() == gold_e[f"light_cache_sha256_epoch{a.epoch}"], rank
+        if not a.fused:
+            ctx.generate_slice()
+    else:
+        ctx = nx.EpochContext(a.epoch, local, rank=rank, world=world, deferred=a.fused)
     share = ctx.dag_share_bytes
     first, last = sharding.dag_slice(ctx.dag_num_items, rank, world)
     assert share == sharding.dag_share_items(ctx.dag_num_items, world) * 256
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if a.fused:
-        handles = [None] * world
-        dist.all_gather_object(handles, ctx.ipc_handle())
+        if a.shell:
+            handles = None  # peers already mapped
+        else:
+            handles = [None] * world
+            dist.all_gather_object(handles, ctx.ipc_handle())
         torch.cuda.synchronize()
         dist.barrier()
         e0.record()

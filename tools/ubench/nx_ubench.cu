@@ -73,8 +73,9 @@ __global__ void __launch_bounds__(1024, 1) int_kernel(u32* out, int iters, u32 s
 }
 
 // ------------------------------------------------------------------------------------------------ lds
-// Each lane does ITER x 8 random reads of a 4096-word table; address chain through the loaded value like K1
-// (index = previous mix word & 4095).  COPIES interleaved replicas as in kawpow_kernel.cuh.
+// Each lane does ITER x 8 random reads of a 4096-word table, the index depending on the values read before (like K1's
+// index = mix word & 4095).  COPIES interleaved replicas as in kawpow_kernel.cuh.  Five integer instructions ride along
+// with each read (LCG, shift, mask, address, merge) - fewer than the ~10 a KawPow round has per read.
 template <int COPIES>
 __global__ void __launch_bounds__(1024, 1) lds_kernel(u32* out, int iters, u32 seed, u64* cycles)
 {
@@ -82,14 +83,22 @@ __global__ void __launch_bounds__(1024, 1) lds_kernel(u32* out, int iters, u32 s
     for (u32 i = threadIdx.x; i < 4096u * COPIES; i += blockDim.x) tab[i] = (i / COPIES) * 2654435761u + seed;
     __syncthreads();
     const u32 rep = (threadIdx.x & 31u) / (32 / COPIES);
-    u32 a[8];
+    // The index of each read mixes a per-lane LCG stream with the values read so far: it depends on the data (as
+    // KawPow's `mix[src] % 4096` does) but cannot fall into a short cycle the way an index fed by the table alone would.
+    u32 a[8], s[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) a[i] = seed * (threadIdx.x * 8 + i + 1);
+    for (int i = 0; i < 8; ++i) {
+        a[i] = seed * (threadIdx.x * 8 + i + 1);
+        s[i] = (seed ^ ((blockIdx.x * blockDim.x + threadIdx.x) * 8u + i) * 2654435761u) | 1u;
+    }
     const u64 t0 = clock64();
 #pragma unroll 1
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] = a[i] * 33u + tab[(a[i] & 4095u) * COPIES + rep];
+        for (int i = 0; i < 8; ++i) {
+            s[i] = s[i] * 1664525u + 1013904223u;  // one multiply-add; the high half of an LCG is a long stream
+            a[i] = a[i] * 33u + tab[((a[i] ^ (s[i] >> 16)) & 4095u) * COPIES + rep];
+        }
     }
     const u64 t1 = clock64();
     u32 x = 0;
