@@ -118,8 +118,11 @@ def test_light_cache_gpu_kernels_match_the_reference_digest(nx, monkeypatch, ker
         c.close()
 
 
-def test_two_gpu_sharded_build_and_search(nx):
-    """Real N=2 path (NCCL all-gather of the DAG slices, sharded search) when the box has two GPUs."""
+@pytest.mark.parametrize("route", [[], ["--fused"], ["--shell", "--fused"], ["--shell"]])
+def test_two_gpu_sharded_build_and_search(nx, route):
+    """Real N=2 paths when the box has two GPUs: the DAG slices exchanged by one NCCL all-gather or by peer stores inside
+    the generating kernel, each with every rank running its own light-cache chain or with ONE chain whose result is
+    broadcast (--shell); then a sharded search.  Every rank checks the reference-made digests."""
     import subprocess
     import sys
 
@@ -127,7 +130,7 @@ def test_two_gpu_sharded_build_and_search(nx):
     if nx.lib.nx_device_count() < 2:
         pytest.skip("needs 2 GPUs")
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-                          "--master-addr", "127.0.0.1", "--master-port", "29533", "tools/multigpu_check.py"],
+                          "--master-addr", "127.0.0.1", "--master-port", "29533", "tools/multigpu_check.py"] + route,
                          cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert '"multigpu_check": "ok"' in out.stdout
