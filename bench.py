@@ -2,10 +2,13 @@
 """bench.py — KawPow nonce-search throughput (MH/s) on B200, against the HBM roofline.
 
 Workload (BASELINE.json configs[1]): KawPow search at the mainnet-sized epoch 448 (4.50 GiB DAG), synthetic
-header hashes keccak256(u64 seed), start nonce = seed << 32, boundary 0 (never hits: pure throughput).
+header hashes keccak256(u64 seed), boundary 0 (never hits: pure throughput).
 A "step" is one pass of the search kernel over one batch of --batch nonces (default 2^24 = 256 GiB of
-algorithmic DAG reads), with a fresh header every step.  The DAG (4.5 GiB) and each step's 256 GiB of random
-reads are far larger than the 126 MB L2, so no L2 flush is needed between steps.
+algorithmic DAG reads).  The device-timed steps share header 1 and each takes the next nonce window (rank g of N
+takes window kN+g); the end-to-end steps pass a fresh header and start nonce from host memory per call.  The DAG
+(4.5 GiB) and each step's 256 GiB of random reads are far larger than the 126 MB L2, so no L2 flush is needed
+between steps.  After the timed region rank 0 also measures the other kernels of the path (`paths`), and at N>1 the
+epoch is built a second time by the other DAG-exchange route (`epoch_build.other_route`).
 
   python bench.py --gpus 1 --steps 20 --warmup 3
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
