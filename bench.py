@@ -498,6 +498,7 @@ def main():
             paths = secondary_paths(nx, ctx, epoch, height, list(range(world)), measured_peak_gbs()[0])
         except Exception as e:  # noqa: BLE001 - an extra must never sink the bench line
             paths = {"error": repr(e)[:300]}
+        torch.cuda.set_device(local)  # the miner made other devices current in this thread
     if dist is not None:
         dist.barrier(group=cpu_group)  # the other ranks wait here on the host while rank 0's miner uses every GPU
 
