@@ -327,3 +327,19 @@ def test_search_stops_scanning_above_a_hit(ctx_of):
     assert sr.solution_found and sr.nonce == start + want
     sr = progpow.search(ctx, 600, hd, boundary, start + last, 1)
     assert sr.solution_found and sr.nonce == start + last
+
+
+def test_batch_kernel_writes_only_its_results(ctx_of):
+    """Every launch shape of the compiled kernel (thin units for small counts, full units, a ragged last unit, warps whose
+    unit lies past the end) stores exactly count x 64 bytes: guard zones on both sides of the device buffer stay intact."""
+    import torch
+    ctx = ctx_of(0)
+    hd = hashlib.sha256(b"guards").digest()
+    guard = 8192
+    for count in (1, 31, 33, 4737, 9473, 65536, 151553, 303105):
+        buf = torch.full((guard + count * 64 + guard,), 0xA5, dtype=torch.uint8, device="cuda:0")
+        progpow.hash_batch_device(ctx, 91, hd, 1 << 50, count, buf.data_ptr() + guard)
+        got = buf.cpu().numpy().tobytes()
+        assert got[:guard] == b"\xa5" * guard and got[guard + count * 64:] == b"\xa5" * guard, count
+        if count <= 65536:
+            assert got[guard:guard + count * 64] == progpow.hash_batch(ctx, 91, hd, 1 << 50, count), count
