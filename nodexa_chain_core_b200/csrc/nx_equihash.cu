@@ -33,9 +33,11 @@ namespace
 constexpr int EQ_MAX_CHUNKS = 12;      // k+1
 constexpr int EQ_COLLIDE_THREADS = 256;
 constexpr int EQ_MAX_CANDIDATES = 8192;
-#ifndef EQ_ROWS_IN_SMEM
-#define EQ_ROWS_IN_SMEM 1  // measured: 1143 Sol/s at (200,9) with the copy, 1071 reading the rows in place
-#endif
+
+// Rows are stored at a stride rounded up to a multiple of 4 words: a row is then read and written as whole 16-byte
+// accesses (a new row goes to a random bucket, so every store of it opens a new 32-byte sector: 3 x 16 B instead of
+// 9 x 4 B is a third of the L2 write operations).
+__host__ __device__ __forceinline__ uint32_t eq_stride(uint32_t live_words) { return (live_words + 3u) & ~3u; }
 
 struct EqParams
 {
@@ -109,7 +111,8 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
         const uint32_t i = g * (uint32_t)p.ipp + (uint32_t)j;
         if (i >= p.N) break;
         uint32_t ch[EQ_MAX_CHUNKS];
-        for (int c = 0; c < p.chunks; ++c) ch[c] = eq_chunk_words(d, j * p.hash_bytes, p.cbl, c);
+#pragma unroll
+        for (int c = 0; c < EQ_MAX_CHUNKS; ++c) ch[c] = c < p.chunks ? eq_chunk_words(d, j * p.hash_bytes, p.cbl, c) : 0u;
         const uint32_t b = p.bucket_bits ? (ch[0] >> 8) : 0u;
         const uint32_t slot = atomicAdd(&bucket_cnt[b], 1u);
         if (slot >= p.slots) {
@@ -117,32 +120,35 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
             continue;
         }
         const uint32_t id = b * p.slots + slot;
-        for (int c = 0; c < p.chunks; ++c) rows[(size_t)id * p.chunks + c] = ch[c];  // round 0: stride = chunks
+        // round 0: chunks live words at a stride rounded up to 4 words, so that a row is whole 16-byte stores
+        const uint32_t st = eq_stride((uint32_t)p.chunks);
+        uint4* dst = reinterpret_cast<uint4*>(rows + (size_t)id * st);
+#pragma unroll
+        for (int q = 0; q < EQ_MAX_CHUNKS / 4; ++q)
+            if ((uint32_t)q * 4u < st) dst[q] = make_uint4(ch[4 * q], ch[4 * q + 1], ch[4 * q + 2], ch[4 * q + 3]);
         leaf[id] = i;
     }
 }
 
 // ---- one round: one CTA per bucket ----
-// Rows of round r carry only the chunks that are still alive, r..k: their stride is S = chunks - r words.
-// dynamic shared memory: [order: slots x u16][key: slots x u16] (+ the bucket's rows, slots x S words, when
-// EQ_ROWS_IN_SMEM; otherwise the rows are read in place - the bucket is one contiguous 10-20 KiB region that stays
-// in L1 - which leaves room for twice as many resident CTAs)
-__global__ void __launch_bounds__(EQ_COLLIDE_THREADS)
+// Rows of round r carry only the chunks that are still alive, r..k: S = chunks - r live words (template parameter, so
+// that a row lives in registers while it is built), stored in global memory at stride eq_stride(S).
+// dynamic shared memory: [the bucket's rows, compact: slots x S words][order: slots x u16][key: slots x u16]
+template <int S>
+__global__ void __launch_bounds__(EQ_COLLIDE_THREADS, 5)  // 5 CTAs per SM is what the shared memory of round 0 allows
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ bucket_cnt,
                   uint32_t* __restrict__ next_rows, uint32_t* __restrict__ next_cnt, uint2* __restrict__ tree,
                   const uint2* __restrict__ prev_tree, uint32_t* __restrict__ cand_count)
 {
-    extern __shared__ uint32_t eq_smem[];
+    extern __shared__ __align__(16) uint32_t eq_smem[];
     __shared__ uint32_t hist[256];
     __shared__ uint32_t start[257];
     __shared__ uint32_t warp_sum[EQ_COLLIDE_THREADS / 32];
-    const uint32_t S = (uint32_t)(p.chunks - r);  // word 0 of a row is chunk r
-#if EQ_ROWS_IN_SMEM
+    constexpr uint32_t ST = (S + 3) & ~3;         // stride of the rows read
+    constexpr uint32_t SO = S - 1;                // live words of the rows written (word 0 = chunk r + 1)
+    constexpr uint32_t STO = (SO + 3) & ~3;       // their stride
     uint32_t* const rs = eq_smem;
     uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * S);
-#else
-    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem);
-#endif
     uint16_t* const key = order + p.slots;
     const uint32_t b = blockIdx.x, t = threadIdx.x;
     const uint32_t cnt = min(bucket_cnt[b], p.slots);
@@ -151,12 +157,19 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     if (cnt == 0) return;
 
     hist[t] = 0;
-    const uint32_t* src = rows + (size_t)base * S;
-#if EQ_ROWS_IN_SMEM
-    for (uint32_t i = t; i < cnt * S; i += EQ_COLLIDE_THREADS) rs[i] = src[i];  // contiguous: the bucket's rows
-#else
-    const uint32_t* const rs = src;
-#endif
+    {   // the bucket's rows: one contiguous region, read as 16-byte words, kept compact in shared memory
+        const uint4* src = reinterpret_cast<const uint4*>(rows + (size_t)base * ST);
+        constexpr uint32_t QPR = ST / 4;  // 16-byte words per row
+        for (uint32_t i = t; i < cnt * QPR; i += EQ_COLLIDE_THREADS) {
+            const uint4 v = src[i];
+            const uint32_t row = i / QPR, w0 = (i % QPR) * 4u;
+            uint32_t* d = rs + row * S + w0;
+            if (w0 + 0 < S) d[0] = v.x;
+            if (w0 + 1 < S) d[1] = v.y;
+            if (w0 + 2 < S) d[2] = v.z;
+            if (w0 + 3 < S) d[3] = v.w;
+        }
+    }
     __syncthreads();
     for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
         const uint32_t kk = rs[i * S] & 0xffu;
@@ -218,7 +231,8 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                 const uint32_t* ra = rs + sa[c] * S;
                 const uint32_t* rb = rs + sb[c] * S;
                 uint32_t any = 0, x1 = 0;
-                for (uint32_t w = 1; w < S; ++w) {  // word w = chunk r + w
+#pragma unroll
+                for (uint32_t w = 1; w < (uint32_t)S; ++w) {  // word w = chunk r + w
                     const uint32_t x = ra[w] ^ rb[w];
                     if (w == 1) x1 = x;
                     any |= x;
@@ -250,8 +264,12 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                         const uint32_t id = nb[c] * p.slots + slot[c];
                         const uint32_t* ra = rs + sa[c] * S;
                         const uint32_t* rb = rs + sb[c] * S;
-                        uint32_t* dst = next_rows + (size_t)id * (S - 1);
-                        for (uint32_t w = 1; w < S; ++w) dst[w - 1] = ra[w] ^ rb[w];
+                        uint32_t o[STO > 0 ? STO : 4];
+#pragma unroll
+                        for (uint32_t w = 0; w < STO; ++w) o[w] = w < SO ? (ra[w + 1] ^ rb[w + 1]) : 0u;
+                        uint4* dst = reinterpret_cast<uint4*>(next_rows + (size_t)id * STO);
+#pragma unroll
+                        for (uint32_t q = 0; q < STO / 4; ++q) dst[q] = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
                         tree[id] = make_uint2(base + sa[c], base + sb[c]);
                     }
                 }
@@ -259,6 +277,26 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                 live |= j[c] < end[c];
             }
         }
+    }
+}
+
+// one instantiation per number of live words (2 .. EQ_MAX_CHUNKS)
+typedef void (*EqCollideFn)(EqParams, int, const uint32_t*, const uint32_t*, uint32_t*, uint32_t*, uint2*, const uint2*, uint32_t*);
+EqCollideFn eq_collide_fn(int live_words)
+{
+    switch (live_words) {
+    case 2: return eq_collide_kernel<2>;
+    case 3: return eq_collide_kernel<3>;
+    case 4: return eq_collide_kernel<4>;
+    case 5: return eq_collide_kernel<5>;
+    case 6: return eq_collide_kernel<6>;
+    case 7: return eq_collide_kernel<7>;
+    case 8: return eq_collide_kernel<8>;
+    case 9: return eq_collide_kernel<9>;
+    case 10: return eq_collide_kernel<10>;
+    case 11: return eq_collide_kernel<11>;
+    case 12: return eq_collide_kernel<12>;
+    default: return nullptr;
     }
 }
 
@@ -494,7 +532,7 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     s->device = device;
     std::memcpy(s->tag, tag, 8);
     const size_t ids = (size_t)p.num_buckets * p.slots;  // row ids per round
-    const size_t row_bytes = ids * p.chunks * 4;
+    const size_t row_bytes = ids * eq_stride((uint32_t)p.chunks) * 4;
     const uint32_t leaves = 1u << k;
     s->smem_bytes = (size_t)p.slots * p.chunks * 4 + (size_t)p.slots * 2 * 2;
     bool ok = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) == cudaSuccess && cudaEventCreate(&s->ev0) == cudaSuccess &&
@@ -508,8 +546,11 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
               cudaMalloc((void**)&s->verdict, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess;
     for (int r = 1; ok && r <= k; ++r)
         ok = cudaMalloc((void**)&s->tree[r], (r == k ? (size_t)EQ_MAX_CANDIDATES : ids) * sizeof(uint2)) == cudaSuccess;
-    if (ok && s->smem_bytes > 48 * 1024)
-        ok = cudaFuncSetAttribute(eq_collide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_bytes) == cudaSuccess;
+    for (int live = 2; ok && live <= p.chunks; ++live) {
+        const size_t smem = (size_t)p.slots * (size_t)live * 4 + (size_t)p.slots * 2 * 2;
+        if (smem > 48 * 1024)
+            ok = cudaFuncSetAttribute(eq_collide_fn(live), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess;
+    }
     if (!ok) {
         set_error("Equihash(%d,%d): device set-up failed: %s", n, k, cudaGetErrorString(cudaGetLastError()));
         nx_equihash_destroy(s);
@@ -550,8 +591,8 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     ++launches;
     for (int r = 0; r < k; ++r) {
         NX_CUDA(cudaMemsetAsync(s->bucket_cnt[(r + 1) & 1], 0, cnt_bytes, s->stream));
-        const size_t smem = (EQ_ROWS_IN_SMEM ? (size_t)p.slots * (size_t)(p.chunks - r) * 4 : 0) + (size_t)p.slots * 2 * 2;
-        eq_collide_kernel<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
+        const size_t smem = (size_t)p.slots * (size_t)(p.chunks - r) * 4 + (size_t)p.slots * 2 * 2;
+        eq_collide_fn(p.chunks - r)<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
             r >= 1 ? s->tree[r] : nullptr, s->cand_count);
         ++launches;
