@@ -133,7 +133,7 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
 // ---- one round: one CTA per bucket ----
 // Rows of round r carry only the chunks that are still alive, r..k: S = chunks - r live words (template parameter, so
 // that a row lives in registers while it is built), stored in global memory at stride eq_stride(S).
-// dynamic shared memory: [the bucket's rows, compact: slots x S words][order: slots x u16][key: slots x u16]
+// dynamic shared memory: [the bucket's rows without their sort key: slots x (S-1) words][order: slots x u16][key: slots x u16]
 template <int S>
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS, 5)  // 5 CTAs per SM is what the shared memory of round 0 allows
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ bucket_cnt,
@@ -147,8 +147,9 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     constexpr uint32_t ST = (S + 3) & ~3;         // stride of the rows read
     constexpr uint32_t SO = S - 1;                // live words of the rows written (word 0 = chunk r + 1)
     constexpr uint32_t STO = (SO + 3) & ~3;       // their stride
+    // shared memory keeps only what a pair needs: the SO words behind the sort key (word 0 goes into key[] and is done)
     uint32_t* const rs = eq_smem;
-    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * S);
+    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SO);
     uint16_t* const key = order + p.slots;
     const uint32_t b = blockIdx.x, t = threadIdx.x;
     const uint32_t cnt = min(bucket_cnt[b], p.slots);
@@ -157,24 +158,26 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     if (cnt == 0) return;
 
     hist[t] = 0;
-    {   // the bucket's rows: one contiguous region, read as 16-byte words, kept compact in shared memory
+    __syncthreads();
+    {   // the bucket's rows: one contiguous region, read as 16-byte words
         const uint4* src = reinterpret_cast<const uint4*>(rows + (size_t)base * ST);
         constexpr uint32_t QPR = ST / 4;  // 16-byte words per row
         for (uint32_t i = t; i < cnt * QPR; i += EQ_COLLIDE_THREADS) {
             const uint4 v = src[i];
             const uint32_t row = i / QPR, w0 = (i % QPR) * 4u;
-            uint32_t* d = rs + row * S + w0;
-            if (w0 + 0 < S) d[0] = v.x;
-            if (w0 + 1 < S) d[1] = v.y;
-            if (w0 + 2 < S) d[2] = v.z;
-            if (w0 + 3 < S) d[3] = v.w;
+            const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) {
+                const uint32_t w = w0 + q;
+                if (w == 0) {
+                    const uint32_t kk = vv[q] & 0xffu;  // the low 8 bits of chunk r: the counting-sort key
+                    key[row] = (uint16_t)kk;
+                    atomicAdd(&hist[kk], 1u);
+                } else if (w < (uint32_t)S) {
+                    rs[row * SO + (w - 1)] = vv[q];
+                }
+            }
         }
-    }
-    __syncthreads();
-    for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
-        const uint32_t kk = rs[i * S] & 0xffu;
-        key[i] = (uint16_t)kk;
-        atomicAdd(&hist[kk], 1u);
     }
     __syncthreads();
     {   // exclusive scan of the 256 bins: thread t owns bin t
@@ -198,10 +201,11 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) order[atomicAdd(&hist[key[i]], 1u)] = (uint16_t)i;
     __syncthreads();
     // Sorted position i pairs with every later position of its key group.  A thread owns positions t, t+256, ...
-    // (up to EQ_CURSORS of them) and advances them in lock step: per step it first issues the slot-reserving
-    // atomics of all its live cursors, and only then uses the returned slots - so several global atomics per
-    // thread are in flight instead of one (their latency is what this kernel waits on).
-    constexpr int EQ_CURSORS = 4;
+    // (EQ_CURSORS of them at a time; a bucket holds about 512 rows, so two cover it) and advances them in lock step:
+    // per step it XORs the pair of every live cursor into registers and issues the slot-reserving atomic, and only
+    // then uses the returned slots - so the atomics of a thread are in flight together (their latency is what this
+    // kernel waits on) and a pair's rows are read from shared memory once.
+    constexpr int EQ_CURSORS = 2;
     for (uint32_t i0 = t; i0 < cnt; i0 += EQ_COLLIDE_THREADS * EQ_CURSORS) {
         uint32_t sa[EQ_CURSORS], j[EQ_CURSORS], end[EQ_CURSORS];
         bool live = false;
@@ -221,21 +225,21 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
         }
         while (live) {
             uint32_t slot[EQ_CURSORS], nb[EQ_CURSORS], sb[EQ_CURSORS];
+            uint32_t o[EQ_CURSORS][STO];
             bool emit[EQ_CURSORS];
-            // phase A: decide and reserve
+            // phase A: XOR, decide and reserve
 #pragma unroll
             for (int c = 0; c < EQ_CURSORS; ++c) {
                 emit[c] = false;
                 if (j[c] >= end[c]) continue;
                 sb[c] = order[j[c]];
-                const uint32_t* ra = rs + sa[c] * S;
-                const uint32_t* rb = rs + sb[c] * S;
-                uint32_t any = 0, x1 = 0;
+                const uint32_t* ra = rs + sa[c] * SO;
+                const uint32_t* rb = rs + sb[c] * SO;
+                uint32_t any = 0;
 #pragma unroll
-                for (uint32_t w = 1; w < (uint32_t)S; ++w) {  // word w = chunk r + w
-                    const uint32_t x = ra[w] ^ rb[w];
-                    if (w == 1) x1 = x;
-                    any |= x;
+                for (uint32_t w = 0; w < STO; ++w) {  // word w = chunk r + 1 + w
+                    o[c][w] = w < SO ? (ra[w] ^ rb[w]) : 0u;
+                    any |= o[c][w];
                 }
                 if (last) {
                     if (any != 0) continue;  // the last round must cancel both remaining chunks
@@ -246,7 +250,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                     slot[c] = atomicAdd(cand_count, 1u);
                 } else {
                     if (any == 0) continue;  // identical remainders: the two subtrees share their index set
-                    nb[c] = p.bucket_bits ? (x1 >> 8) : 0u;
+                    nb[c] = p.bucket_bits ? (o[c][0] >> 8) : 0u;
                     slot[c] = atomicAdd(&next_cnt[nb[c]], 1u);
                 }
                 emit[c] = true;
@@ -262,14 +266,10 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                         atomicAdd(cand_count + 1, 1u);  // a row that did not fit its bucket is lost: counted, reported
                     } else {
                         const uint32_t id = nb[c] * p.slots + slot[c];
-                        const uint32_t* ra = rs + sa[c] * S;
-                        const uint32_t* rb = rs + sb[c] * S;
-                        uint32_t o[STO > 0 ? STO : 4];
-#pragma unroll
-                        for (uint32_t w = 0; w < STO; ++w) o[w] = w < SO ? (ra[w + 1] ^ rb[w + 1]) : 0u;
                         uint4* dst = reinterpret_cast<uint4*>(next_rows + (size_t)id * STO);
 #pragma unroll
-                        for (uint32_t q = 0; q < STO / 4; ++q) dst[q] = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+                        for (uint32_t q = 0; q < STO / 4; ++q)
+                            dst[q] = make_uint4(o[c][4 * q], o[c][4 * q + 1], o[c][4 * q + 2], o[c][4 * q + 3]);
                         tree[id] = make_uint2(base + sa[c], base + sb[c]);
                     }
                 }
@@ -547,8 +547,10 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     for (int r = 1; ok && r <= k; ++r)
         ok = cudaMalloc((void**)&s->tree[r], (r == k ? (size_t)EQ_MAX_CANDIDATES : ids) * sizeof(uint2)) == cudaSuccess;
     for (int live = 2; ok && live <= p.chunks; ++live) {
-        const size_t smem = (size_t)p.slots * (size_t)live * 4 + (size_t)p.slots * 2 * 2;
-        if (smem > 48 * 1024)
+        // every instantiation that will run gets its own opt-in (the 48 KiB default counts the 2 KiB of static shared
+        // memory too, so sizes just below it need the attribute as well)
+        const size_t smem = (size_t)p.slots * (size_t)(live - 1) * 4 + (size_t)p.slots * 2 * 2;
+        if (smem > 40 * 1024)
             ok = cudaFuncSetAttribute(eq_collide_fn(live), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess;
     }
     if (!ok) {
@@ -591,10 +593,11 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     ++launches;
     for (int r = 0; r < k; ++r) {
         NX_CUDA(cudaMemsetAsync(s->bucket_cnt[(r + 1) & 1], 0, cnt_bytes, s->stream));
-        const size_t smem = (size_t)p.slots * (size_t)(p.chunks - r) * 4 + (size_t)p.slots * 2 * 2;
+        const size_t smem = (size_t)p.slots * (size_t)(p.chunks - r - 1) * 4 + (size_t)p.slots * 2 * 2;
         eq_collide_fn(p.chunks - r)<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
             r >= 1 ? s->tree[r] : nullptr, s->cand_count);
+        NX_CUDA(cudaGetLastError());
         ++launches;
     }
     uint32_t stats[2] = {0, 0};
