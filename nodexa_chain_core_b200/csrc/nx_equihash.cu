@@ -38,6 +38,13 @@ constexpr int EQ_MAX_CANDIDATES = 8192;
 // accesses (a new row goes to a random bucket, so every store of it opens a new 32-byte sector: 3 x 16 B instead of
 // 9 x 4 B is a third of the L2 write operations).
 __host__ __device__ __forceinline__ uint32_t eq_stride(uint32_t live_words) { return (live_words + 3u) & ~3u; }
+// Shared-memory stride of a staged row (its S-1 words behind the sort key): rounded up to an even number of words so
+// that a row is read as 8- or 16-byte accesses - except for the widest rows, where the extra word per row would cost a
+// resident CTA (round 0 of (200,9): 9 words x 1024 slots is what lets five CTAs share an SM).
+__host__ __device__ constexpr uint32_t eq_smem_stride(int live_words)
+{
+    return live_words >= 10 ? (uint32_t)(live_words - 1) : (uint32_t)(live_words & ~1);  // S-1, or S-1 rounded up to even
+}
 
 struct EqParams
 {
@@ -100,19 +107,30 @@ __device__ void eq_string_chunks(const EqParams& p, const EqMid& mid, uint32_t i
 }
 
 // ---- round 0: N strings, each appended to the bucket its chunk 0 selects ----
+// NN, KK > 0: the parameter set is known at compile time, so every byte position of every chunk is a literal and the
+// digest and the chunks stay in registers (the generic form indexes the digest dynamically: 112 bytes of local memory
+// per thread and twice the time).  NN = 0: any (n, k) the engine accepts.
+template <int NN, int KK>
 __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__ rows, uint32_t* __restrict__ leaf,
                                    uint32_t* __restrict__ bucket_cnt, uint32_t* __restrict__ dropped)
 {
+    const int chunks = NN ? KK + 1 : p.chunks;
+    const int cbl = NN ? NN / (KK + 1) : p.cbl;
+    const int ipp = NN ? 512 / NN : p.ipp;
+    const int hash_bytes = NN ? NN / 8 : p.hash_bytes;
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;  // one digest per thread
-    if (g >= (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp) return;  // N need not be a multiple of 512/n
+    if (g >= (p.N + (uint32_t)ipp - 1) / (uint32_t)ipp) return;  // N need not be a multiple of 512/n
     uint64_t d[8];
     eq_digest_words(mid, g, d);
-    for (int j = 0; j < p.ipp; ++j) {
-        const uint32_t i = g * (uint32_t)p.ipp + (uint32_t)j;
+    const uint32_t st = eq_stride((uint32_t)chunks);  // live words at a stride of whole 16-byte stores
+#pragma unroll
+    for (int j = 0; j < (NN ? 512 / NN : 8); ++j) {
+        if (j >= ipp) break;
+        const uint32_t i = g * (uint32_t)ipp + (uint32_t)j;
         if (i >= p.N) break;
         uint32_t ch[EQ_MAX_CHUNKS];
 #pragma unroll
-        for (int c = 0; c < EQ_MAX_CHUNKS; ++c) ch[c] = c < p.chunks ? eq_chunk_words(d, j * p.hash_bytes, p.cbl, c) : 0u;
+        for (int c = 0; c < EQ_MAX_CHUNKS; ++c) ch[c] = c < chunks ? eq_chunk_words(d, j * hash_bytes, cbl, c) : 0u;
         const uint32_t b = p.bucket_bits ? (ch[0] >> 8) : 0u;
         const uint32_t slot = atomicAdd(&bucket_cnt[b], 1u);
         if (slot >= p.slots) {
@@ -120,8 +138,6 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
             continue;
         }
         const uint32_t id = b * p.slots + slot;
-        // round 0: chunks live words at a stride rounded up to 4 words, so that a row is whole 16-byte stores
-        const uint32_t st = eq_stride((uint32_t)p.chunks);
         uint4* dst = reinterpret_cast<uint4*>(rows + (size_t)id * st);
 #pragma unroll
         for (int q = 0; q < EQ_MAX_CHUNKS / 4; ++q)
@@ -130,10 +146,42 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
     }
 }
 
+typedef void (*EqGenerateFn)(EqParams, EqMid, uint32_t*, uint32_t*, uint32_t*, uint32_t*);
+EqGenerateFn eq_generate_fn(int n, int k)
+{
+    if (n == 200 && k == 9) return eq_generate_kernel<200, 9>;
+    if (n == 144 && k == 5) return eq_generate_kernel<144, 5>;
+    if (n == 192 && k == 7) return eq_generate_kernel<192, 7>;
+    if (n == 96 && k == 5) return eq_generate_kernel<96, 5>;
+    return eq_generate_kernel<0, 0>;
+}
+
+// one staged row out of shared memory, in the widest accesses its stride allows
+template <uint32_t SP>
+__device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
+{
+    if (SP % 4 == 0) {
+#pragma unroll
+        for (uint32_t q = 0; q < SP / 4; ++q) {
+            const uint4 v = reinterpret_cast<const uint4*>(r)[q];
+            out[4 * q] = v.x, out[4 * q + 1] = v.y, out[4 * q + 2] = v.z, out[4 * q + 3] = v.w;
+        }
+    } else if (SP % 2 == 0) {
+#pragma unroll
+        for (uint32_t q = 0; q < SP / 2; ++q) {
+            const uint2 v = reinterpret_cast<const uint2*>(r)[q];
+            out[2 * q] = v.x, out[2 * q + 1] = v.y;
+        }
+    } else {
+#pragma unroll
+        for (uint32_t q = 0; q < SP; ++q) out[q] = r[q];
+    }
+}
+
 // ---- one round: one CTA per bucket ----
 // Rows of round r carry only the chunks that are still alive, r..k: S = chunks - r live words (template parameter, so
 // that a row lives in registers while it is built), stored in global memory at stride eq_stride(S).
-// dynamic shared memory: [the bucket's rows without their sort key: slots x (S-1) words][order: slots x u16][key: slots x u16]
+// dynamic shared memory: [the bucket's rows without their sort key: slots x eq_smem_stride(S) words][order: slots x u16][key: slots x u16]
 template <int S>
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS, 5)  // 5 CTAs per SM is what the shared memory of round 0 allows
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ bucket_cnt,
@@ -147,9 +195,10 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     constexpr uint32_t ST = (S + 3) & ~3;         // stride of the rows read
     constexpr uint32_t SO = S - 1;                // live words of the rows written (word 0 = chunk r + 1)
     constexpr uint32_t STO = (SO + 3) & ~3;       // their stride
+    constexpr uint32_t SP = eq_smem_stride(S);    // stride of a row in shared memory (even where that is free: 8/16-byte reads)
     // shared memory keeps only what a pair needs: the SO words behind the sort key (word 0 goes into key[] and is done)
     uint32_t* const rs = eq_smem;
-    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SO);
+    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SP);
     uint16_t* const key = order + p.slots;
     const uint32_t b = blockIdx.x, t = threadIdx.x;
     const uint32_t cnt = min(bucket_cnt[b], p.slots);
@@ -162,19 +211,31 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     {   // the bucket's rows: one contiguous region, read as 16-byte words
         const uint4* src = reinterpret_cast<const uint4*>(rows + (size_t)base * ST);
         constexpr uint32_t QPR = ST / 4;  // 16-byte words per row
-        for (uint32_t i = t; i < cnt * QPR; i += EQ_COLLIDE_THREADS) {
-            const uint4 v = src[i];
-            const uint32_t row = i / QPR, w0 = (i % QPR) * 4u;
-            const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+        // four loads in flight per thread before the first is used: the copy is a chain of global-memory latencies
+        constexpr uint32_t U = 4;
+        for (uint32_t i0 = t; i0 < cnt * QPR; i0 += EQ_COLLIDE_THREADS * U) {
+            uint4 v[U];
 #pragma unroll
-            for (uint32_t q = 0; q < 4; ++q) {
-                const uint32_t w = w0 + q;
-                if (w == 0) {
-                    const uint32_t kk = vv[q] & 0xffu;  // the low 8 bits of chunk r: the counting-sort key
-                    key[row] = (uint16_t)kk;
-                    atomicAdd(&hist[kk], 1u);
-                } else if (w < (uint32_t)S) {
-                    rs[row * SO + (w - 1)] = vv[q];
+            for (uint32_t u = 0; u < U; ++u) {
+                const uint32_t i = i0 + u * EQ_COLLIDE_THREADS;
+                v[u] = i < cnt * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u);
+            }
+#pragma unroll
+            for (uint32_t u = 0; u < U; ++u) {
+                const uint32_t i = i0 + u * EQ_COLLIDE_THREADS;
+                if (i >= cnt * QPR) break;
+                const uint32_t row = i / QPR, w0 = (i % QPR) * 4u;
+                const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+                for (uint32_t q = 0; q < 4; ++q) {
+                    const uint32_t w = w0 + q;
+                    if (w == 0) {
+                        const uint32_t kk = vv[q] & 0xffu;  // the low 8 bits of chunk r: the counting-sort key
+                        key[row] = (uint16_t)kk;
+                        atomicAdd(&hist[kk], 1u);
+                    } else if (w < (uint32_t)S) {
+                        rs[row * SP + (w - 1)] = vv[q];
+                    }
                 }
             }
         }
@@ -233,12 +294,13 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                 emit[c] = false;
                 if (j[c] >= end[c]) continue;
                 sb[c] = order[j[c]];
-                const uint32_t* ra = rs + sa[c] * SO;
-                const uint32_t* rb = rs + sb[c] * SO;
+                uint32_t xa[SP], xb[SP];
+                eq_load_row<SP>(rs + sa[c] * SP, xa);
+                eq_load_row<SP>(rs + sb[c] * SP, xb);
                 uint32_t any = 0;
 #pragma unroll
                 for (uint32_t w = 0; w < STO; ++w) {  // word w = chunk r + 1 + w
-                    o[c][w] = w < SO ? (ra[w] ^ rb[w]) : 0u;
+                    o[c][w] = w < SO ? (xa[w] ^ xb[w]) : 0u;
                     any |= o[c][w];
                 }
                 if (last) {
@@ -549,7 +611,7 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     for (int live = 2; ok && live <= p.chunks; ++live) {
         // every instantiation that will run gets its own opt-in (the 48 KiB default counts the 2 KiB of static shared
         // memory too, so sizes just below it need the attribute as well)
-        const size_t smem = (size_t)p.slots * (size_t)(live - 1) * 4 + (size_t)p.slots * 2 * 2;
+        const size_t smem = (size_t)p.slots * eq_smem_stride(live) * 4 + (size_t)p.slots * 2 * 2;
         if (smem > 40 * 1024)
             ok = cudaFuncSetAttribute(eq_collide_fn(live), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess;
     }
@@ -589,11 +651,12 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     NX_CUDA(cudaMemsetAsync(s->cand_count, 0, 8, s->stream));
     NX_CUDA(cudaMemsetAsync(s->bucket_cnt[0], 0, cnt_bytes, s->stream));
     const uint32_t digests = (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp;
-    eq_generate_kernel<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0], s->leaf, s->bucket_cnt[0], s->cand_count + 1);
+    eq_generate_fn(p.n, p.k)<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0], s->leaf, s->bucket_cnt[0], s->cand_count + 1);
+    NX_CUDA(cudaGetLastError());
     ++launches;
     for (int r = 0; r < k; ++r) {
         NX_CUDA(cudaMemsetAsync(s->bucket_cnt[(r + 1) & 1], 0, cnt_bytes, s->stream));
-        const size_t smem = (size_t)p.slots * (size_t)(p.chunks - r - 1) * 4 + (size_t)p.slots * 2 * 2;
+        const size_t smem = (size_t)p.slots * eq_smem_stride(p.chunks - r) * 4 + (size_t)p.slots * 2 * 2;
         eq_collide_fn(p.chunks - r)<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
             r >= 1 ? s->tree[r] : nullptr, s->cand_count);
