@@ -24,6 +24,7 @@
 #include "nx_internal.hpp"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace nx
@@ -123,9 +124,9 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
     uint64_t d[8];
     eq_digest_words(mid, g, d);
     const uint32_t st = eq_stride((uint32_t)chunks);  // live words at a stride of whole 16-byte stores
-#pragma unroll
-    for (int j = 0; j < (NN ? 512 / NN : 8); ++j) {
-        if (j >= ipp) break;
+    // specialised: 512/NN iterations, unrolled (every position a literal); generic: ipp iterations (up to 32 for n = 16)
+#pragma unroll(NN ? 512 / NN : 1)
+    for (int j = 0; j < ipp; ++j) {
         const uint32_t i = g * (uint32_t)ipp + (uint32_t)j;
         if (i >= p.N) break;
         uint32_t ch[EQ_MAX_CHUNKS];
@@ -160,13 +161,13 @@ EqGenerateFn eq_generate_fn(int n, int k)
 template <uint32_t SP>
 __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
 {
-    if (SP % 4 == 0) {
+    if constexpr (SP % 4 == 0) {
 #pragma unroll
         for (uint32_t q = 0; q < SP / 4; ++q) {
             const uint4 v = reinterpret_cast<const uint4*>(r)[q];
             out[4 * q] = v.x, out[4 * q + 1] = v.y, out[4 * q + 2] = v.z, out[4 * q + 3] = v.w;
         }
-    } else if (SP % 2 == 0) {
+    } else if constexpr (SP % 2 == 0) {
 #pragma unroll
         for (uint32_t q = 0; q < SP / 2; ++q) {
             const uint2 v = reinterpret_cast<const uint2*>(r)[q];
@@ -620,6 +621,11 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
         nx_equihash_destroy(s);
         return NX_ERR_OOM;
     }
+    if (const char* e = std::getenv("NX_EQ_SWAP"))  // experiment: which ping-pong buffer is read first
+        if (*e == '1') {
+            std::swap(s->rows[0], s->rows[1]);
+            std::swap(s->bucket_cnt[0], s->bucket_cnt[1]);
+        }
     *out = s;
     return NX_OK;
 }
