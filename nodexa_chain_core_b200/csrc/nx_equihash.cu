@@ -34,6 +34,12 @@ namespace
 constexpr int EQ_MAX_CHUNKS = 12;      // k+1
 constexpr int EQ_COLLIDE_THREADS = 256;
 constexpr int EQ_MAX_CANDIDATES = 8192;
+// Bucket slot counters sit EQ_CNT_STRIDE words apart.  Every new row reserves its slot with an atomicAdd on its bucket's
+// counter, 2^21 of them per round; the L2 serialises atomics that hit one line, so the stride decides how many of them run
+// side by side.  NX_EQ_CNT_STRIDE (1, 8 or 32 words; read at create time) is kept as a measurement knob.
+#ifndef EQ_CNT_STRIDE_DEFAULT
+#define EQ_CNT_STRIDE_DEFAULT 8
+#endif
 
 // Rows are stored at a stride rounded up to a multiple of 4 words: a row is then read and written as whole 16-byte
 // accesses (a new row goes to a random bucket, so every store of it opens a new 32-byte sector: 3 x 16 B instead of
@@ -54,6 +60,7 @@ struct EqParams
     int bucket_bits;      // cbl - 8 (0 when cbl == 8)
     uint32_t num_buckets;
     uint32_t slots;       // row slots per bucket: 1024 (mean load 512); 2048 for tiny N, whose single bucket swings widely
+    uint32_t cnt_stride;  // words between the slot counters of neighbouring buckets
 };
 
 // Word-level BLAKE2b tail: the host has absorbed the header up to the last (partial) block; a thread appends its
@@ -133,7 +140,7 @@ __global__ void eq_generate_kernel(EqParams p, EqMid mid, uint32_t* __restrict__
 #pragma unroll
         for (int c = 0; c < EQ_MAX_CHUNKS; ++c) ch[c] = c < chunks ? eq_chunk_words(d, j * hash_bytes, cbl, c) : 0u;
         const uint32_t b = p.bucket_bits ? (ch[0] >> 8) : 0u;
-        const uint32_t slot = atomicAdd(&bucket_cnt[b], 1u);
+        const uint32_t slot = atomicAdd(&bucket_cnt[b * p.cnt_stride], 1u);
         if (slot >= p.slots) {
             atomicAdd(dropped, 1u);
             continue;
@@ -202,7 +209,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SP);
     uint16_t* const key = order + p.slots;
     const uint32_t b = blockIdx.x, t = threadIdx.x;
-    const uint32_t cnt = min(bucket_cnt[b], p.slots);
+    const uint32_t cnt = min(bucket_cnt[b * p.cnt_stride], p.slots);
     const bool last = r == p.k - 1;
     const uint32_t base = b * p.slots;
     if (cnt == 0) return;
@@ -314,7 +321,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
                 } else {
                     if (any == 0) continue;  // identical remainders: the two subtrees share their index set
                     nb[c] = p.bucket_bits ? (o[c][0] >> 8) : 0u;
-                    slot[c] = atomicAdd(&next_cnt[nb[c]], 1u);
+                    slot[c] = atomicAdd(&next_cnt[nb[c] * p.cnt_stride], 1u);
                 }
                 emit[c] = true;
             }
@@ -473,6 +480,7 @@ bool eq_make_params(EqParams& p, int n, int k)
     p.bucket_bits = cbl - 8;
     p.num_buckets = 1u << p.bucket_bits;
     p.slots = p.N <= (1u << 12) ? 2048u : 1024u;
+    p.cnt_stride = EQ_CNT_STRIDE_DEFAULT;
     return true;
 }
 
@@ -591,6 +599,10 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     NX_CUDA(cudaSetDevice(device));
     nx_equihash* s = new (std::nothrow) nx_equihash;
     if (!s) return NX_ERR_OOM;
+    if (const char* e = std::getenv("NX_EQ_CNT_STRIDE")) {
+        const int v = std::atoi(e);
+        if (v == 1 || v == 8 || v == 32) p.cnt_stride = (uint32_t)v;
+    }
     s->p = p;
     s->device = device;
     std::memcpy(s->tag, tag, 8);
@@ -601,8 +613,8 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     bool ok = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) == cudaSuccess && cudaEventCreate(&s->ev0) == cudaSuccess &&
               cudaEventCreate(&s->ev1) == cudaSuccess && cudaMalloc((void**)&s->rows[0], row_bytes) == cudaSuccess &&
               cudaMalloc((void**)&s->rows[1], row_bytes) == cudaSuccess &&
-              cudaMalloc((void**)&s->bucket_cnt[0], (size_t)p.num_buckets * 4) == cudaSuccess &&
-              cudaMalloc((void**)&s->bucket_cnt[1], (size_t)p.num_buckets * 4) == cudaSuccess &&
+              cudaMalloc((void**)&s->bucket_cnt[0], (size_t)p.num_buckets * p.cnt_stride * 4) == cudaSuccess &&
+              cudaMalloc((void**)&s->bucket_cnt[1], (size_t)p.num_buckets * p.cnt_stride * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->leaf, ids * 4) == cudaSuccess && cudaMalloc((void**)&s->cand_count, 8) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_indices, (size_t)EQ_MAX_CANDIDATES * leaves * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_valid, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess &&
@@ -622,9 +634,9 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
         return NX_ERR_OOM;
     }
     if (const char* e = std::getenv("NX_EQ_SWAP"))  // experiment: which ping-pong buffer is read first
-        if (*e == '1') {
-            std::swap(s->rows[0], s->rows[1]);
-            std::swap(s->bucket_cnt[0], s->bucket_cnt[1]);
+        {
+            if (*e == '1' || *e == '3') std::swap(s->rows[0], s->rows[1]);
+            if (*e == '1' || *e == '2') std::swap(s->bucket_cnt[0], s->bucket_cnt[1]);
         }
     *out = s;
     return NX_OK;
@@ -651,7 +663,7 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     }
     const int k = p.k;
     int launches = 0;
-    const size_t cnt_bytes = (size_t)p.num_buckets * 4;
+    const size_t cnt_bytes = (size_t)p.num_buckets * p.cnt_stride * 4;
 
     NX_CUDA(cudaEventRecord(s->ev0, s->stream));
     NX_CUDA(cudaMemsetAsync(s->cand_count, 0, 8, s->stream));
