@@ -192,7 +192,7 @@ __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
 // dynamic shared memory: [the bucket's rows without their sort key: slots x eq_smem_stride(S) words][order: slots x u16][key: slots x u16]
 template <int S>
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS, 5)  // 5 CTAs per SM is what the shared memory of round 0 allows
-eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ bucket_cnt,
+eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t* __restrict__ bucket_cnt,
                   uint32_t* __restrict__ next_rows, uint32_t* __restrict__ next_cnt, uint2* __restrict__ tree,
                   const uint2* __restrict__ prev_tree, uint32_t* __restrict__ cand_count)
 {
@@ -210,6 +210,10 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
     uint16_t* const key = order + p.slots;
     const uint32_t b = blockIdx.x, t = threadIdx.x;
     const uint32_t cnt = min(bucket_cnt[b * p.cnt_stride], p.slots);
+    // This CTA is the only reader of its bucket's counter, and the array it sits in is the one the NEXT round appends
+    // to: leave it at zero, so that no memset is needed between rounds (or between solves).
+    __syncthreads();
+    if (t == 0) bucket_cnt[b * p.cnt_stride] = 0u;
     const bool last = r == p.k - 1;
     const uint32_t base = b * p.slots;
     if (cnt == 0) return;
@@ -351,7 +355,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, const ui
 }
 
 // one instantiation per number of live words (2 .. EQ_MAX_CHUNKS)
-typedef void (*EqCollideFn)(EqParams, int, const uint32_t*, const uint32_t*, uint32_t*, uint32_t*, uint2*, const uint2*, uint32_t*);
+typedef void (*EqCollideFn)(EqParams, int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint2*, const uint2*, uint32_t*);
 EqCollideFn eq_collide_fn(int live_words)
 {
     switch (live_words) {
@@ -379,12 +383,12 @@ struct EqTrees
 };
 
 __global__ void eq_recover_kernel(EqParams p, EqTrees trees, const uint32_t* __restrict__ cand_count, uint32_t cand_cap,
-                                  uint32_t* __restrict__ out_indices, uint32_t* __restrict__ out_valid)
+                                  uint32_t cand_base, uint32_t* __restrict__ out_indices, uint32_t* __restrict__ out_valid)
 {
     __shared__ uint32_t idx[512];
     __shared__ uint32_t tmp[512];
     __shared__ int ok;
-    const uint32_t cand = blockIdx.x;
+    const uint32_t cand = cand_base + blockIdx.x;
     const uint32_t leaves = 1u << p.k;
     const uint32_t t = threadIdx.x;
     if (cand >= min(*cand_count, cand_cap)) return;
@@ -540,6 +544,7 @@ struct nx_equihash
     int last_launches = 0;
     uint32_t last_candidates = 0;
     uint32_t last_dropped = 0;  // rows/candidates lost to a full bucket in the last solve (0 in normal operation)
+    bool counters_clean = false;  // both slot-counter arrays are known to be all zero
     std::mutex mu;
 };
 
@@ -667,13 +672,18 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
 
     NX_CUDA(cudaEventRecord(s->ev0, s->stream));
     NX_CUDA(cudaMemsetAsync(s->cand_count, 0, 8, s->stream));
-    NX_CUDA(cudaMemsetAsync(s->bucket_cnt[0], 0, cnt_bytes, s->stream));
+    // The slot counters are left at zero by the kernels that read them (eq_collide_kernel), so a solve normally starts
+    // on clean arrays; only after a solve that did not run to its end are they cleared here.
+    if (!s->counters_clean) {
+        NX_CUDA(cudaMemsetAsync(s->bucket_cnt[0], 0, cnt_bytes, s->stream));
+        NX_CUDA(cudaMemsetAsync(s->bucket_cnt[1], 0, cnt_bytes, s->stream));
+    }
+    s->counters_clean = false;
     const uint32_t digests = (p.N + (uint32_t)p.ipp - 1) / (uint32_t)p.ipp;
     eq_generate_fn(p.n, p.k)<<<(digests + 127) / 128, 128, 0, s->stream>>>(p, mid, s->rows[0], s->leaf, s->bucket_cnt[0], s->cand_count + 1);
     NX_CUDA(cudaGetLastError());
     ++launches;
     for (int r = 0; r < k; ++r) {
-        NX_CUDA(cudaMemsetAsync(s->bucket_cnt[(r + 1) & 1], 0, cnt_bytes, s->stream));
         const size_t smem = (size_t)p.slots * eq_smem_stride(p.chunks - r) * 4 + (size_t)p.slots * 2 * 2;
         eq_collide_fn(p.chunks - r)<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
@@ -681,23 +691,37 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
         NX_CUDA(cudaGetLastError());
         ++launches;
     }
+    // Candidates are expanded without waiting for their count: a first launch covers the usual handful (its CTAs look
+    // at the count themselves), and only a header with more than EQ_RECOVER_FIRST candidates costs a second launch.
+    constexpr uint32_t EQ_RECOVER_FIRST = 64;
+    const uint32_t leaves = 1u << k;
+    EqTrees trees;
+    for (int i = 0; i < EQ_MAX_CHUNKS; ++i) trees.t[i] = s->tree[i];
+    trees.leaf = s->leaf;
+    eq_recover_kernel<<<EQ_RECOVER_FIRST, leaves, 0, s->stream>>>(p, trees, s->cand_count, EQ_MAX_CANDIDATES, 0u, s->cand_indices,
+                                                                 s->cand_valid);
+    NX_CUDA(cudaGetLastError());
+    ++launches;
+    NX_CUDA(cudaEventRecord(s->ev1, s->stream));
     uint32_t stats[2] = {0, 0};
     NX_CUDA(cudaMemcpyAsync(stats, s->cand_count, 8, cudaMemcpyDeviceToHost, s->stream));
     NX_CUDA(cudaStreamSynchronize(s->stream));
+    s->counters_clean = true;
     s->last_dropped = stats[1] + (stats[0] > EQ_MAX_CANDIDATES ? stats[0] - EQ_MAX_CANDIDATES : 0);
     const uint32_t ncand = std::min<uint32_t>(stats[0], EQ_MAX_CANDIDATES);
-    const uint32_t leaves = 1u << k;
-    if (ncand) {
-        EqTrees trees;
-        for (int i = 0; i < EQ_MAX_CHUNKS; ++i) trees.t[i] = s->tree[i];
-        trees.leaf = s->leaf;
-        eq_recover_kernel<<<ncand, leaves, 0, s->stream>>>(p, trees, s->cand_count, EQ_MAX_CANDIDATES, s->cand_indices, s->cand_valid);
-        ++launches;
-        NX_CUDA(cudaGetLastError());
-    }
-    NX_CUDA(cudaEventRecord(s->ev1, s->stream));
-    NX_CUDA(cudaStreamSynchronize(s->stream));
     NX_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
+    if (ncand > EQ_RECOVER_FIRST) {
+        NX_CUDA(cudaEventRecord(s->ev0, s->stream));
+        eq_recover_kernel<<<ncand - EQ_RECOVER_FIRST, leaves, 0, s->stream>>>(p, trees, s->cand_count, EQ_MAX_CANDIDATES,
+                                                                             EQ_RECOVER_FIRST, s->cand_indices, s->cand_valid);
+        NX_CUDA(cudaGetLastError());
+        ++launches;
+        NX_CUDA(cudaEventRecord(s->ev1, s->stream));
+        NX_CUDA(cudaStreamSynchronize(s->stream));
+        float more = 0;
+        NX_CUDA(cudaEventElapsedTime(&more, s->ev0, s->ev1));
+        s->last_ms += more;
+    }
     s->last_launches = launches;
     s->last_candidates = ncand;
     if (ncand == 0) return NX_OK;
