@@ -386,7 +386,7 @@ __global__ void eq_recover_kernel(EqParams p, EqTrees trees, const uint32_t* __r
                                   uint32_t cand_base, uint32_t* __restrict__ out_indices, uint32_t* __restrict__ out_valid)
 {
     __shared__ uint32_t idx[512];
-    __shared__ uint32_t tmp[512];
+    __shared__ uint32_t tmp[1024];
     __shared__ int ok;
     const uint32_t cand = cand_base + blockIdx.x;
     const uint32_t leaves = 1u << p.k;
@@ -412,12 +412,24 @@ __global__ void eq_recover_kernel(EqParams p, EqTrees trees, const uint32_t* __r
         if (swap) idx[t ^ width] = v;  // exchange the two halves of the node
         __syncthreads();
     }
-    // distinct indices: every thread compares its index with all later ones
+    // distinct indices: every thread puts its index into a small open-addressing table; meeting itself means a duplicate
     const uint32_t mine = idx[t];
-    tmp[t] = mine;
+    tmp[t] = 0xffffffffu;
+    tmp[t + leaves] = 0xffffffffu;  // table of 2 x leaves entries (indices are < 2^25, so all-ones is free as "empty")
     __syncthreads();
-    for (uint32_t j = t + 1; j < leaves; ++j)
-        if (tmp[j] == mine) ok = 0;
+    {
+        const uint32_t mask = 2u * leaves - 1u;
+        uint32_t slot = (mine * 2654435761u) >> 7 & mask;
+        for (;;) {
+            const uint32_t old = atomicCAS(&tmp[slot], 0xffffffffu, mine);
+            if (old == 0xffffffffu) break;
+            if (old == mine) {
+                ok = 0;
+                break;
+            }
+            slot = (slot + 1u) & mask;
+        }
+    }
     __syncthreads();
     out_indices[(size_t)cand * leaves + t] = idx[t];
     if (t == 0) out_valid[cand] = (uint32_t)ok;

@@ -230,3 +230,49 @@ def test_sharded_slices_copied_together_give_the_reference_dag(nx, world):
         assert c0.checksum() == want
     finally:
         c0.close()
+
+
+def test_one_chain_for_the_job_shell_contexts_on_one_device(nx):
+    """The multi-process epoch build in which ONE rank runs the light-cache chain (nx_epoch_create_shell /
+    nx_epoch_build_light_cache / nx_epoch_adopt_light_cache), with both "ranks" on cuda:0 and a device-to-device copy
+    standing in for the NCCL broadcast: same light cache (sha256 against the reference's), same DAG digest on both, through
+    the fused route on one pair of contexts and the slice + gather route on another; and the state checks in between."""
+    import torch
+    e = golden("epochs.json")
+    want = golden("dag_digest.json")["0"]["weighted_sum"]
+    for route in ("fused", "slice"):
+        a = nx.EpochContext(0, 0, rank=0, world=2, shell=True)
+        b = nx.EpochContext(0, 0, rank=1, world=2, shell=True)
+        try:
+            with pytest.raises(nx.NxError):      # no light cache yet: nothing may be generated from it
+                a.generate_slice()
+            with pytest.raises(nx.NxError):
+                a.generate_fused_peers([a.dag_ptr, b.dag_ptr])
+            a.build_light_cache()                # the one chain of the job
+            with pytest.raises(nx.NxError):      # a second light cache for the same context is a state error
+                a.build_light_cache()
+            b.light_tensor().copy_(a.light_tensor())   # stands for ncclBroadcast into nx_epoch_light_ptr()
+            torch.cuda.synchronize()
+            b.adopt_light_cache()
+            with pytest.raises(nx.NxError):
+                b.adopt_light_cache()
+            for c in (a, b):
+                assert hashlib.sha256(c.light_cache).hexdigest() == e["light_cache_sha256_epoch0"]
+            if route == "fused":
+                ptrs = [a.dag_ptr, b.dag_ptr]
+                a.generate_fused_peers(ptrs)
+                b.generate_fused_peers(ptrs)
+            else:
+                a.generate_slice()
+                b.generate_slice()
+                share = a.dag_share_bytes
+                a.dag_tensor()[share:2 * share].copy_(b.dag_tensor()[share:2 * share])
+                b.dag_tensor()[:share].copy_(a.dag_tensor()[:share])
+                torch.cuda.synchronize()
+            a.finalize()
+            b.finalize()
+            assert a.checksum() == want and b.checksum() == want
+            assert hashlib.sha256(struct.pack("<4096I", *b.l1_cache)).hexdigest() == e["l1_sha256_epoch0"]
+        finally:
+            a.close()
+            b.close()
