@@ -851,13 +851,14 @@ int nx_kawpow_search(const nx_epoch* c, int block_number, const uint8_t header_h
     int launches = 0;
     uint64_t done = 0;
     while (done < iterations) {
-        for (int q = 0; q < SEARCH_QUEUE && done < iterations; ++q, done += SEARCH_BATCH) {
+        for (int q = 0; q < SEARCH_QUEUE && done < iterations; ++q) {
             const uint64_t n = iterations - done < SEARCH_BATCH ? iterations - done : SEARCH_BATCH;
             if ((rc = nx_kawpow_search_enqueue(c, block_number, header_hash, boundary, start_nonce + done, n)) != NX_OK) {
                 nx_search_result drop;
                 nx_kawpow_search_sync(c, &drop);  // leave no launch pending behind an error
                 return rc;
             }
+            done += n;  // ends exactly at `iterations`: no wrap for ranges that reach up to 2^64 - 1
         }
         if ((rc = nx_kawpow_search_sync(c, out)) != NX_OK) return rc;
         total_ms += c->last_kernel_ms;

@@ -1,6 +1,6 @@
 #!/bin/bash
 # round 2, GPU session 1: parity of the persistent kernel, then ceilings and micro-benchmarks
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.max.sm,power.limit --format=csv > gpurun_out/s1_gpu.txt
 timeout 900 python -m pytest tests/test_gpu_kawpow.py tests/test_gpu_miner.py tests/test_gpu_verify.py -x -q -m gpu > gpurun_out/s1_pytest_kawpow.log 2>&1

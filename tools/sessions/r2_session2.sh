@@ -1,6 +1,6 @@
 #!/bin/bash
 # round 2, GPU session 2 (one GPU): full GPU test suite, LDS microbenchmark, K7 in-flight knob, bench line with paths, ncu
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -x -q -m gpu --timeout 400 --durations=12 -s > gpurun_out/s2_pytest_all.log 2>&1
 echo "pytest all rc=$?" > gpurun_out/s2_status.txt

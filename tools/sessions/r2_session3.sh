@@ -1,7 +1,7 @@
 #!/bin/bash
 # round 2, GPU session 3 (N GPUs, default 2): the multi-process epoch build (one chain + broadcast) and the scaling bench line
 N=${1:-2}
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=index,name --format=csv > gpurun_out/s3_gpus.txt
 if [ "$N" = "2" ]; then

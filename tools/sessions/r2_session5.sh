@@ -1,6 +1,6 @@
 #!/bin/bash
 # round 2, GPU session 5 (one GPU): Equihash engine with 16-byte row accesses, full GPU suite
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_equihash.py -x -q -m gpu --timeout 300 > gpurun_out/s5_pytest_eq.log 2>&1
 echo "pytest equihash rc=$?" > gpurun_out/s5_status.txt

@@ -1,6 +1,6 @@
 #!/bin/bash
 # round 2, GPU session 8 (one GPU): Equihash - which buffer makes every other round slow, and the counter stride
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_equihash.py -x -q -m gpu --timeout 300 > gpurun_out/s8_pytest_eq.log 2>&1
 echo "pytest equihash rc=$?" > gpurun_out/s8_status.txt
