@@ -189,7 +189,11 @@ __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
 // ---- one round: one CTA per bucket ----
 // Rows of round r carry only the chunks that are still alive, r..k: S = chunks - r live words (template parameter, so
 // that a row lives in registers while it is built), stored in global memory at stride eq_stride(S).
-// dynamic shared memory: [the bucket's rows without their sort key: slots x eq_smem_stride(S) words][order: slots x u16][key: slots x u16]
+// Rows that collide on chunk r share its low 8 bits inside a bucket, so while the bucket is staged every row is pushed
+// onto the chain of its key (one shared-memory atomicExch per row: head[key] <- row, next[row] <- old head); a row
+// then pairs with everything behind it in its chain.  (Round 1 counting-sorted the bucket instead: two shared-memory
+// atomics per row, a 256-bin scan and three more barriers - the atomics alone were a third of a round.)
+// dynamic shared memory: [the bucket's rows without their sort key: slots x eq_smem_stride(S) words][next: slots x u16]
 template <int S>
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS, 5)  // 5 CTAs per SM is what the shared memory of round 0 allows
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t* __restrict__ bucket_cnt,
@@ -197,19 +201,18 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
                   const uint2* __restrict__ prev_tree, uint32_t* __restrict__ cand_count)
 {
     extern __shared__ __align__(16) uint32_t eq_smem[];
-    __shared__ uint32_t hist[256];
-    __shared__ uint32_t start[257];
-    __shared__ uint32_t warp_sum[EQ_COLLIDE_THREADS / 32];
+    __shared__ uint32_t head[256];
+    constexpr uint32_t NIL = 0xffffu;
     constexpr uint32_t ST = (S + 3) & ~3;         // stride of the rows read
     constexpr uint32_t SO = S - 1;                // live words of the rows written (word 0 = chunk r + 1)
     constexpr uint32_t STO = (SO + 3) & ~3;       // their stride
     constexpr uint32_t SP = eq_smem_stride(S);    // stride of a row in shared memory (even where that is free: 8/16-byte reads)
-    // shared memory keeps only what a pair needs: the SO words behind the sort key (word 0 goes into key[] and is done)
+    // shared memory keeps only what a pair needs: the SO words behind the sort key (word 0 picks the chain and is done)
     uint32_t* const rs = eq_smem;
-    uint16_t* const order = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SP);
-    uint16_t* const key = order + p.slots;
+    uint16_t* const next = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SP);
     const uint32_t b = blockIdx.x, t = threadIdx.x;
     const uint32_t cnt = min(bucket_cnt[b * p.cnt_stride], p.slots);
+    head[t] = NIL;
     // This CTA is the only reader of its bucket's counter, and the array it sits in is the one the NEXT round appends
     // to: leave it at zero, so that no memset is needed between rounds (or between solves).
     __syncthreads();
@@ -218,8 +221,6 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
     const uint32_t base = b * p.slots;
     if (cnt == 0) return;
 
-    hist[t] = 0;
-    __syncthreads();
     {   // the bucket's rows: one contiguous region, read as 16-byte words
         const uint4* src = reinterpret_cast<const uint4*>(rows + (size_t)base * ST);
         constexpr uint32_t QPR = ST / 4;  // 16-byte words per row
@@ -242,9 +243,8 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
                 for (uint32_t q = 0; q < 4; ++q) {
                     const uint32_t w = w0 + q;
                     if (w == 0) {
-                        const uint32_t kk = vv[q] & 0xffu;  // the low 8 bits of chunk r: the counting-sort key
-                        key[row] = (uint16_t)kk;
-                        atomicAdd(&hist[kk], 1u);
+                        // the low 8 bits of chunk r: push the row onto that key's chain
+                        next[row] = (uint16_t)atomicExch(&head[vv[q] & 0xffu], row);
                     } else if (w < (uint32_t)S) {
                         rs[row * SP + (w - 1)] = vv[q];
                     }
@@ -253,48 +253,21 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
         }
     }
     __syncthreads();
-    {   // exclusive scan of the 256 bins: thread t owns bin t
-        const uint32_t v = hist[t];
-        uint32_t inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
-            if ((t & 31u) >= (uint32_t)o) inc += u;
-        }
-        if ((t & 31u) == 31u) warp_sum[t >> 5] = inc;
-        __syncthreads();
-        uint32_t off = 0;
-        for (uint32_t w = 0; w < (t >> 5); ++w) off += warp_sum[w];
-        start[t] = off + inc - v;
-        if (t == EQ_COLLIDE_THREADS - 1) start[256] = off + inc;
-        __syncthreads();
-        hist[t] = start[t];  // running insert positions
-    }
-    __syncthreads();
-    for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) order[atomicAdd(&hist[key[i]], 1u)] = (uint16_t)i;
-    __syncthreads();
-    // Sorted position i pairs with every later position of its key group.  A thread owns positions t, t+256, ...
-    // (EQ_CURSORS of them at a time; a bucket holds about 512 rows, so two cover it) and advances them in lock step:
-    // per step it XORs the pair of every live cursor into registers and issues the slot-reserving atomic, and only
-    // then uses the returned slots - so the atomics of a thread are in flight together (their latency is what this
-    // kernel waits on) and a pair's rows are read from shared memory once.
+    // Row i pairs with every row behind it in its chain.  A thread owns rows t, t+256, ... (EQ_CURSORS of them at a
+    // time; a bucket holds about 512 rows, so two cover it) and advances them in lock step: per step it XORs the pair of
+    // every live cursor into registers and issues the slot-reserving atomic, and only then uses the returned slots - so
+    // the atomics of a thread are in flight together (their latency is what this kernel waits on) and a pair's rows are
+    // read from shared memory once.
     constexpr int EQ_CURSORS = 2;
     for (uint32_t i0 = t; i0 < cnt; i0 += EQ_COLLIDE_THREADS * EQ_CURSORS) {
-        uint32_t sa[EQ_CURSORS], j[EQ_CURSORS], end[EQ_CURSORS];
+        uint32_t sa[EQ_CURSORS], j[EQ_CURSORS];
         bool live = false;
 #pragma unroll
         for (int c = 0; c < EQ_CURSORS; ++c) {
             const uint32_t i = i0 + (uint32_t)c * EQ_COLLIDE_THREADS;
-            if (i < cnt) {
-                sa[c] = order[i];
-                end[c] = start[key[sa[c]] + 1u];
-                j[c] = i + 1;
-            } else {
-                sa[c] = 0;
-                end[c] = 0;
-                j[c] = 1;
-            }
-            live |= j[c] < end[c];
+            sa[c] = i < cnt ? i : 0u;
+            j[c] = i < cnt ? (uint32_t)next[i] : NIL;
+            live |= j[c] != NIL;
         }
         while (live) {
             uint32_t slot[EQ_CURSORS], nb[EQ_CURSORS], sb[EQ_CURSORS];
@@ -304,8 +277,8 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
 #pragma unroll
             for (int c = 0; c < EQ_CURSORS; ++c) {
                 emit[c] = false;
-                if (j[c] >= end[c]) continue;
-                sb[c] = order[j[c]];
+                sb[c] = j[c];
+                if (j[c] == NIL) continue;
                 uint32_t xa[SP], xb[SP];
                 eq_load_row<SP>(rs + sa[c] * SP, xa);
                 eq_load_row<SP>(rs + sb[c] * SP, xb);
@@ -329,7 +302,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
                 }
                 emit[c] = true;
             }
-            // phase B: use the reserved slots
+            // phase B: use the reserved slots, step along the chains
             live = false;
 #pragma unroll
             for (int c = 0; c < EQ_CURSORS; ++c) {
@@ -347,8 +320,8 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
                         tree[id] = make_uint2(base + sa[c], base + sb[c]);
                     }
                 }
-                ++j[c];
-                live |= j[c] < end[c];
+                if (j[c] != NIL) j[c] = next[j[c]];
+                live |= j[c] != NIL;
             }
         }
     }
@@ -641,7 +614,7 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     for (int live = 2; ok && live <= p.chunks; ++live) {
         // every instantiation that will run gets its own opt-in (the 48 KiB default counts the 2 KiB of static shared
         // memory too, so sizes just below it need the attribute as well)
-        const size_t smem = (size_t)p.slots * eq_smem_stride(live) * 4 + (size_t)p.slots * 2 * 2;
+        const size_t smem = (size_t)p.slots * eq_smem_stride(live) * 4 + (size_t)p.slots * 2;
         if (smem > 40 * 1024)
             ok = cudaFuncSetAttribute(eq_collide_fn(live), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess;
     }
@@ -696,7 +669,7 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     NX_CUDA(cudaGetLastError());
     ++launches;
     for (int r = 0; r < k; ++r) {
-        const size_t smem = (size_t)p.slots * eq_smem_stride(p.chunks - r) * 4 + (size_t)p.slots * 2 * 2;
+        const size_t smem = (size_t)p.slots * eq_smem_stride(p.chunks - r) * 4 + (size_t)p.slots * 2;
         eq_collide_fn(p.chunks - r)<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
             r >= 1 ? s->tree[r] : nullptr, s->cand_count);
