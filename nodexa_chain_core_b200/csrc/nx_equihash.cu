@@ -34,6 +34,7 @@ namespace
 constexpr int EQ_MAX_CHUNKS = 12;      // k+1
 constexpr int EQ_COLLIDE_THREADS = 256;
 constexpr int EQ_MAX_CANDIDATES = 8192;
+constexpr uint32_t EQ_RECOVER_FIRST = 64;  // candidates expanded (and copied to the host) before their count is known
 // Bucket slot counters sit EQ_CNT_STRIDE words apart.  Every new row reserves its slot with an atomicAdd on its bucket's
 // counter, 2^21 of them per round; the L2 serialises atomics that hit one line, so the stride decides how many of them run
 // side by side.  NX_EQ_CNT_STRIDE (1, 8 or 32 words; read at create time) is kept as a measurement knob.
@@ -530,6 +531,7 @@ struct nx_equihash
     uint32_t last_candidates = 0;
     uint32_t last_dropped = 0;  // rows/candidates lost to a full bucket in the last solve (0 in normal operation)
     bool counters_clean = false;  // both slot-counter arrays are known to be all zero
+    uint32_t* host_first = nullptr;  // pinned: {valid[F], indices[F x 2^k], stats[2]} of the first F candidates, one async copy each
     std::mutex mu;
 };
 
@@ -558,6 +560,7 @@ void nx_equihash_destroy(nx_equihash* s)
     if (s->cand_indices) cudaFree(s->cand_indices);
     if (s->cand_valid) cudaFree(s->cand_valid);
     if (s->verdict) cudaFree(s->verdict);
+    if (s->host_first) cudaFreeHost(s->host_first);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -608,7 +611,8 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
               cudaMalloc((void**)&s->leaf, ids * 4) == cudaSuccess && cudaMalloc((void**)&s->cand_count, 8) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_indices, (size_t)EQ_MAX_CANDIDATES * leaves * 4) == cudaSuccess &&
               cudaMalloc((void**)&s->cand_valid, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess &&
-              cudaMalloc((void**)&s->verdict, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess;
+              cudaMalloc((void**)&s->verdict, (size_t)EQ_MAX_CANDIDATES * 4) == cudaSuccess &&
+              cudaMallocHost((void**)&s->host_first, ((size_t)EQ_RECOVER_FIRST * (leaves + 1) + 2) * 4) == cudaSuccess;
     for (int r = 1; ok && r <= k; ++r)
         ok = cudaMalloc((void**)&s->tree[r], (r == k ? (size_t)EQ_MAX_CANDIDATES : ids) * sizeof(uint2)) == cudaSuccess;
     for (int live = 2; ok && live <= p.chunks; ++live) {
@@ -678,7 +682,6 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     }
     // Candidates are expanded without waiting for their count: a first launch covers the usual handful (its CTAs look
     // at the count themselves), and only a header with more than EQ_RECOVER_FIRST candidates costs a second launch.
-    constexpr uint32_t EQ_RECOVER_FIRST = 64;
     const uint32_t leaves = 1u << k;
     EqTrees trees;
     for (int i = 0; i < EQ_MAX_CHUNKS; ++i) trees.t[i] = s->tree[i];
@@ -688,7 +691,12 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     NX_CUDA(cudaGetLastError());
     ++launches;
     NX_CUDA(cudaEventRecord(s->ev1, s->stream));
-    uint32_t stats[2] = {0, 0};
+    // results of the first launch and the counts travel in the same queue: one wait for the whole solve
+    uint32_t* const h_valid = s->host_first;
+    uint32_t* const h_idx = s->host_first + EQ_RECOVER_FIRST;
+    uint32_t* const stats = s->host_first + (size_t)EQ_RECOVER_FIRST * (leaves + 1);
+    NX_CUDA(cudaMemcpyAsync(h_valid, s->cand_valid, (size_t)EQ_RECOVER_FIRST * 4, cudaMemcpyDeviceToHost, s->stream));
+    NX_CUDA(cudaMemcpyAsync(h_idx, s->cand_indices, (size_t)EQ_RECOVER_FIRST * leaves * 4, cudaMemcpyDeviceToHost, s->stream));
     NX_CUDA(cudaMemcpyAsync(stats, s->cand_count, 8, cudaMemcpyDeviceToHost, s->stream));
     NX_CUDA(cudaStreamSynchronize(s->stream));
     s->counters_clean = true;
@@ -711,8 +719,14 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     s->last_candidates = ncand;
     if (ncand == 0) return NX_OK;
     std::vector<uint32_t> valid(ncand), idx((size_t)ncand * leaves);
-    NX_CUDA(cudaMemcpy(valid.data(), s->cand_valid, (size_t)ncand * 4, cudaMemcpyDeviceToHost));
-    NX_CUDA(cudaMemcpy(idx.data(), s->cand_indices, (size_t)ncand * leaves * 4, cudaMemcpyDeviceToHost));
+    const uint32_t have = std::min<uint32_t>(ncand, EQ_RECOVER_FIRST);  // already on the host
+    std::memcpy(valid.data(), h_valid, (size_t)have * 4);
+    std::memcpy(idx.data(), h_idx, (size_t)have * leaves * 4);
+    if (ncand > have) {
+        NX_CUDA(cudaMemcpy(valid.data() + have, s->cand_valid + have, (size_t)(ncand - have) * 4, cudaMemcpyDeviceToHost));
+        NX_CUDA(cudaMemcpy(idx.data() + (size_t)have * leaves, s->cand_indices + (size_t)have * leaves,
+                           (size_t)(ncand - have) * leaves * 4, cudaMemcpyDeviceToHost));
+    }
     const size_t sb = ((size_t)1 << k) * (size_t)(p.cbl + 1) / 8;
     std::vector<std::vector<uint8_t>> sols;
     for (uint32_t c = 0; c < ncand; ++c) {
