@@ -13,10 +13,11 @@
 // GPU mapping: rows LIVE in buckets.  Bucket b of round r holds the rows whose chunk r has top bits b
 // (cbl-8 of them, so a bucket's mean load is N / 2^(cbl-8) = 512 rows whatever (n,k) is); a row id is
 // bucket*slots + slot.  A round is ONE kernel, one CTA per bucket: the bucket's rows are copied into shared
-// memory (contiguous, coalesced), counting-sorted by the remaining 8 bits of the chunk, and every colliding pair
-// is XOR-ed and appended straight to the bucket its NEXT chunk selects (one atomic slot counter per bucket, so the
-// atomics are spread over thousands of addresses) together with a two-id back-reference.  The generator does the
-// same with the BLAKE2b strings, so there is no separate scatter pass.  Candidates of the last round are
+// memory (contiguous, 16-byte loads) and chained by the remaining 8 bits of the chunk on the way in, and every
+// colliding pair is XOR-ed and appended straight to the bucket its NEXT chunk selects (one atomic slot counter per
+// bucket, each in a 32-byte sector of its own because the L2 serialises atomics per line) as whole 16-byte stores,
+// together with a two-id back-reference.  The generator does the same with the BLAKE2b strings, so there is no
+// separate scatter pass.  Candidates of the last round are
 // expanded, canonically ordered and checked for distinct indices by one CTA each; an independent validator
 // kernel recomputes the BLAKE2b strings of a solution and re-checks every rule.
 #include "../../include/nx_equihash.h"
