@@ -323,7 +323,17 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
         os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: the container's hostname need not resolve
-        cpu_group = dist.new_group(backend="gloo")  # host-side waits that must not keep a spinning NCCL kernel on the GPU
+        cpu_group = dist.new_group(backend="gloo")
+        # NCCL builds its communicator and its per-collective connections lazily (0.3-1 s on first use): that is process
+        # start-up, not epoch build, so every collective the build uses is run once here, before any clock starts
+        warm = torch.zeros(1 << 20, dtype=torch.uint8, device=f"cuda:{local}")
+        dist.broadcast(warm, src=0)
+        dist.all_gather_into_tensor(torch.empty(world * 1024, dtype=torch.uint8, device=f"cuda:{local}"), warm[:1024])
+        dist.all_gather_object([None] * world, b"\0" * 64)
+        dist.all_reduce(warm[:8])
+        torch.cuda.synchronize()
+        dist.barrier()
+        del warm  # host-side waits that must not keep a spinning NCCL kernel on the GPU
 
     epoch, height = args.epoch, args.epoch * 7500
 
