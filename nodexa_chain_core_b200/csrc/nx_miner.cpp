@@ -119,7 +119,17 @@ int build_contexts(const std::vector<int>& devices, int epoch, std::vector<nx_ep
                 if (rcs[i] != NX_OK) return true;
             return false;
         };
-        run_all([&](size_t i) { return nx_epoch_create_deferred(epoch, devices[i], (int)i, (int)n, light.data(), &out[i]); });
+        // test hook: NX_MINER_INJECT_CREATE_FAIL=<index> makes that entry's context creation fail (stands for an
+        // allocation that does not fit): the build must stop before any fused kernel runs
+        long fail_create = -1;
+        if (const char* e = std::getenv("NX_MINER_INJECT_CREATE_FAIL")) fail_create = std::strtol(e, nullptr, 10);
+        run_all([&](size_t i) {
+            if ((long)i == fail_create) {
+                set_error("injected failure (NX_MINER_INJECT_CREATE_FAIL)");
+                return (int)NX_ERR_OOM;
+            }
+            return nx_epoch_create_deferred(epoch, devices[i], (int)i, (int)n, light.data(), &out[i]);
+        });
         std::vector<void*> bases(n, nullptr);
         for (size_t i = 0; i < n; ++i) bases[i] = out[i] ? nx_epoch_dag_ptr(out[i]) : nullptr;
         if (!any_failed()) run_all([&](size_t i) { return nx_epoch_generate_fused_peers(out[i], bases.data()); });

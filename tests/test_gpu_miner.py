@@ -191,3 +191,26 @@ def test_unbounded_try_count_scans_until_the_hit(nx):
         assert want.solution_found
         got = m.search(0, hd, boundary, 1, 2**64 - 2)  # start + iterations stays below 2^64: the reference's loop runs
         assert got == want
+
+
+def test_fused_build_on_one_device_and_a_rank_that_fails(nx, monkeypatch):
+    """The miner's fused multi-GPU DAG build (each device generates 1/N and stores it into every device's buffer) runs
+    on a 1-GPU box when the same device is listed twice.  When one entry's context cannot be created, the whole build
+    must be given up BEFORE the generating kernels run - they would store through a buffer that does not exist - with
+    an error, no fault on the device, and a later build must work and hash correctly."""
+    hd = bytes(32)
+    kat_boundary = bytes.fromhex("00" + "ff" * 31)
+    with nx.Miner([0, 0]) as m:
+        assert m.device_count == 2
+        monkeypatch.setenv("NX_MINER_INJECT_CREATE_FAIL", "1")
+        with pytest.raises(nx.NxError) as e:
+            m.set_epoch(0)
+        assert "injected failure" in str(e.value)
+        monkeypatch.delenv("NX_MINER_INJECT_CREATE_FAIL")
+        m.set_epoch(0)                                         # the device is healthy: same miner, clean build
+        m.set_batch(16)
+        kat = m.search(0, hd, kat_boundary, 300, 100)          # kawpow_tests.cpp:109-140 over two contexts of one GPU
+        assert kat.solution_found and kat.nonce == 395
+    with nx.Miner([0]) as one:
+        one.set_batch(16)
+        assert one.search(0, hd, kat_boundary, 300, 100) == kat
