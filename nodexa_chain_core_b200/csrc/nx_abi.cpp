@@ -4,6 +4,7 @@
 
 #include <chrono>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <map>
 #include <vector>
@@ -918,8 +919,13 @@ static int nx_kawpow_hash_many_body(const nx_epoch* cc, const nx_hash_record* re
         std::memcpy(recs[i].header, records[i].header_hash, 32);
         recs[i].nonce = records[i].nonce;
         recs[i].program_slot = it->second;
-        recs[i].pad = 0;
+        recs[i].out_index = (uint32_t)i;
     }
+    // The two half-warps of a warp interpret one record each: when both belong to the same period they take the same
+    // branches of the op dispatch.  Group the records by period (results still land in the caller's order).
+    if (slot_of.size() < n)
+        std::stable_sort(recs.begin(), recs.end(),
+                         [](const KawpowRecord& a, const KawpowRecord& b) { return a.program_slot < b.program_slot; });
     std::vector<uint32_t> progs(slot_of.size() * 36 * 4);
     for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);
 
@@ -1082,7 +1088,7 @@ int nx_test_hash_many_guarded(const nx_epoch* cc, const nx_hash_record* records,
             std::memcpy(recs[i].header, records[i].header_hash, 32);
             recs[i].nonce = records[i].nonce;
             recs[i].program_slot = it->second;
-            recs[i].pad = 0;
+            recs[i].out_index = (uint32_t)i;
         }
         std::vector<uint32_t> progs(slot_of.size() * 36 * 4);
         for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);

@@ -95,7 +95,7 @@ struct KawpowRecord
     uint32_t header[8];
     uint64_t nonce;
     uint32_t program_slot;  // index into the packed program table of this launch
-    uint32_t pad;
+    uint32_t out_index;     // where this record's {final, mix} go in the output array (the caller's record order)
 };
 void kawpow_pack_program(uint64_t prog_seed, uint32_t out[36 * 4]);
 int kawpow_interp_launch(const void* dag, uint32_t dag_items, const KawpowRecord* recs_dev, uint32_t n_recs,

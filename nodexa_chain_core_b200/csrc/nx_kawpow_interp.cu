@@ -144,7 +144,7 @@ kawpow_interp_kernel(const uint4* __restrict__ dag, FastMod32 fm, const KawpowRe
     NX_PAD_LAST(st);
     nxk_f800(st);
     if (live && lane == 0) {
-        uint4* o = reinterpret_cast<uint4*>(out + (size_t)rec_idx * 16u);
+        uint4* o = reinterpret_cast<uint4*>(out + (size_t)rec.out_index * 16u);  // records arrive grouped by period
         o[0] = make_uint4(st[0], st[1], st[2], st[3]);
         o[1] = make_uint4(st[4], st[5], st[6], st[7]);
         o[2] = make_uint4(dg[0], dg[1], dg[2], dg[3]);
