@@ -188,6 +188,13 @@ __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
     }
 }
 
+// Resident CTAs per SM the collide kernel is compiled for: 5 is what the shared memory of the widest rows allows
+// (9 words x 1024 slots); narrower rows leave room for a sixth if the kernel keeps to 40 registers.
+#ifndef EQ_COLLIDE_BLOCKS_NARROW
+#define EQ_COLLIDE_BLOCKS_NARROW 6
+#endif
+#define EQ_COLLIDE_BLOCKS(S) ((S) >= 9 ? 5 : EQ_COLLIDE_BLOCKS_NARROW)
+
 // ---- one round: one CTA per bucket ----
 // Rows of round r carry only the chunks that are still alive, r..k: S = chunks - r live words (template parameter, so
 // that a row lives in registers while it is built), stored in global memory at stride eq_stride(S).
@@ -197,7 +204,7 @@ __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
 // atomics per row, a 256-bin scan and three more barriers - the atomics alone were a third of a round.)
 // dynamic shared memory: [the bucket's rows without their sort key: slots x eq_smem_stride(S) words][next: slots x u16]
 template <int S>
-__global__ void __launch_bounds__(EQ_COLLIDE_THREADS, 5)  // 5 CTAs per SM is what the shared memory of round 0 allows
+__global__ void __launch_bounds__(EQ_COLLIDE_THREADS, EQ_COLLIDE_BLOCKS(S))
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t* __restrict__ bucket_cnt,
                   uint32_t* __restrict__ next_rows, uint32_t* __restrict__ next_cnt, uint2* __restrict__ tree,
                   const uint2* __restrict__ prev_tree, uint32_t* __restrict__ cand_count)
