@@ -189,11 +189,12 @@ __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
 }
 
 // Resident CTAs per SM the collide kernel is compiled for: 5 is what the shared memory of the widest rows allows
-// (9 words x 1024 slots); narrower rows leave room for a sixth if the kernel keeps to 40 registers.
+// (9 words x 1024 slots); rows of 7 words and fewer leave room for a sixth if the kernel keeps to 40 registers
+// (measured at (200,9): 78 -> 70, 76 -> 68, 66 -> 62, 62 -> 59 us for 7, 6, 5, 4 words).
 #ifndef EQ_COLLIDE_BLOCKS_NARROW
 #define EQ_COLLIDE_BLOCKS_NARROW 6
 #endif
-#define EQ_COLLIDE_BLOCKS(S) ((S) >= 9 ? 5 : EQ_COLLIDE_BLOCKS_NARROW)
+#define EQ_COLLIDE_BLOCKS(S) ((S) >= 8 ? 5 : EQ_COLLIDE_BLOCKS_NARROW)  // measured: 8-word rows are slower with six (89 vs 76 us)
 
 // ---- one round: one CTA per bucket ----
 // Rows of round r carry only the chunks that are still alive, r..k: S = chunks - r live words (template parameter, so
