@@ -890,23 +890,13 @@ int nx_kawpow_verify(const nx_epoch* c, int block_number, const uint8_t header_h
     return std::memcmp(r.mix_hash, mix_hash, 32) == 0 ? 1 : 0;
 }
 
-static int nx_kawpow_hash_many_body(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host)
+// Device-side records and packed programs for n caller records (all inside the context's epoch): one packed
+// program per distinct period, recs[i].out_index = i.  Shared by nx_kawpow_hash_many and its guarded test twin.
+static int build_interp_records(const nx_epoch* c, const nx_hash_record* records, size_t n, std::vector<KawpowRecord>& recs,
+                                std::vector<uint32_t>& progs, size_t* n_periods)
 {
-    nx_epoch* c = const_cast<nx_epoch*>(cc);
-    int rc = check_ctx(c, 0);
-    if (rc != NX_OK) return rc;
-    if ((!records || !out_host) && n) {
-        set_error("null argument");
-        return NX_ERR_INVALID;
-    }
-    if (n == 0) return NX_OK;
-    if (n > 0x7fffffffu / 16) {
-        set_error("too many records in one call");
-        return NX_ERR_INVALID;
-    }
-    // one packed program per distinct period in the batch
     std::map<uint64_t, uint32_t> slot_of;
-    std::vector<KawpowRecord> recs(n);
+    recs.resize(n);
     for (size_t i = 0; i < n; ++i) {
         const int bn = records[i].block_number;
         if (bn < 0 || bn / NX_EPOCH_LENGTH != c->epoch) {
@@ -921,13 +911,35 @@ static int nx_kawpow_hash_many_body(const nx_epoch* cc, const nx_hash_record* re
         recs[i].program_slot = it->second;
         recs[i].out_index = (uint32_t)i;
     }
+    progs.assign(slot_of.size() * 36 * 4, 0u);
+    for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);
+    *n_periods = slot_of.size();
+    return NX_OK;
+}
+
+static int nx_kawpow_hash_many_body(const nx_epoch* cc, const nx_hash_record* records, size_t n, uint8_t* out_host)
+{
+    nx_epoch* c = const_cast<nx_epoch*>(cc);
+    int rc = check_ctx(c, 0);
+    if (rc != NX_OK) return rc;
+    if ((!records || !out_host) && n) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    if (n == 0) return NX_OK;
+    if (n > 0x7fffffffu / 16) {
+        set_error("too many records in one call");
+        return NX_ERR_INVALID;
+    }
+    std::vector<KawpowRecord> recs;
+    std::vector<uint32_t> progs;
+    size_t n_periods = 0;
+    if ((rc = build_interp_records(c, records, n, recs, progs, &n_periods)) != NX_OK) return rc;
     // The two half-warps of a warp interpret one record each: when both belong to the same period they take the same
     // branches of the op dispatch.  Group the records by period (results still land in the caller's order).
-    if (slot_of.size() < n)
+    if (n_periods < n)
         std::stable_sort(recs.begin(), recs.end(),
                          [](const KawpowRecord& a, const KawpowRecord& b) { return a.program_slot < b.program_slot; });
-    std::vector<uint32_t> progs(slot_of.size() * 36 * 4);
-    for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);
 
     std::lock_guard<std::recursive_mutex> lk(c->mu);
     NX_CUDA(cudaSetDevice(c->device));
@@ -1074,24 +1086,10 @@ int nx_test_hash_many_guarded(const nx_epoch* cc, const nx_hash_record* records,
             set_error("bad argument");
             return NX_ERR_INVALID;
         }
-        std::map<uint64_t, uint32_t> slot_of;
-        std::vector<KawpowRecord> recs(n);
-        for (size_t i = 0; i < n; ++i) {
-            const int bn = records[i].block_number;
-            if (bn < 0 || bn / NX_EPOCH_LENGTH != c->epoch) {
-                set_error("record %zu: block %d is not in this context's epoch %d", i, bn, c->epoch);
-                return NX_ERR_INVALID;
-            }
-            const uint64_t seed = (uint64_t)(bn / NX_PERIOD_LENGTH);
-            auto it = slot_of.find(seed);
-            if (it == slot_of.end()) it = slot_of.emplace(seed, (uint32_t)slot_of.size()).first;
-            std::memcpy(recs[i].header, records[i].header_hash, 32);
-            recs[i].nonce = records[i].nonce;
-            recs[i].program_slot = it->second;
-            recs[i].out_index = (uint32_t)i;
-        }
-        std::vector<uint32_t> progs(slot_of.size() * 36 * 4);
-        for (const auto& kv : slot_of) kawpow_pack_program(kv.first, progs.data() + (size_t)kv.second * 36 * 4);
+        std::vector<KawpowRecord> recs;
+        std::vector<uint32_t> progs;
+        size_t n_periods = 0;
+        if ((rc = build_interp_records(c, records, n, recs, progs, &n_periods)) != NX_OK) return rc;
 
         constexpr size_t G = 4096;
         const size_t sizes[3] = {n * sizeof(KawpowRecord), progs.size() * 4, n * 64};
