@@ -10,11 +10,13 @@
 #include <unistd.h>
 #include <nvrtc.h>
 
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <future>
 #include <map>
 #include <memory>
 #include <sstream>
@@ -228,6 +230,125 @@ bool kawpow_program_is_cached(int device, uint64_t prog_seed, uint32_t dag_items
     return g_cache.count(std::make_tuple(device, prog_seed, dag_items)) != 0;
 }
 
+// The cubin of (prog_seed, dag_items): from this process's map, else from NX_PROGRAM_CACHE_DIR, else compiled now.
+// One NVRTC run serves every device of the process.  g_compile_mu guards the maps only: the compilation itself runs
+// unlocked, so different periods compile side by side (a background prefetch never delays a foreground request for
+// another period), while a second request for a period that is being compiled waits for that run instead of repeating it.
+namespace
+{
+std::map<std::pair<uint64_t, uint32_t>, std::shared_future<int>> g_inflight;
+}
+
+static int obtain_cubin(uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<const std::vector<char>>* out)
+{
+    const auto ckey = std::make_pair(prog_seed, dag_items);
+    std::promise<int> mine;
+    {
+        std::unique_lock<std::mutex> lk(g_compile_mu);
+        for (;;) {
+            auto it = g_cubins.find(ckey);
+            if (it != g_cubins.end()) {
+                *out = it->second;
+                return NX_OK;
+            }
+            auto fl = g_inflight.find(ckey);
+            if (fl == g_inflight.end()) break;
+            std::shared_future<int> other = fl->second;
+            lk.unlock();
+            const int rc = other.get();  // somebody else is compiling exactly this
+            lk.lock();
+            if (rc != NX_OK && !g_cubins.count(ckey)) {
+                set_error("compilation of period %llu failed in another thread", (unsigned long long)prog_seed);
+                return rc;
+            }
+        }
+        g_inflight[ckey] = mine.get_future().share();
+    }
+    auto fresh = std::make_shared<std::vector<char>>();
+    int rc = NX_OK;
+    const char* arch_env = std::getenv("NX_KAWPOW_ARCH");
+    const std::string path = cache_path(prog_seed, dag_items, arch_env && *arch_env ? arch_env : "sm_100a");
+    if (!path.empty()) {
+        std::ifstream f(path, std::ios::binary);
+        if (f) fresh->assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
+        // a file that is not a whole ELF image (foreign, truncated by a crash) is ignored and rewritten
+        if (fresh->size() < 64 || std::memcmp(fresh->data(), "\x7f" "ELF", 4) != 0) fresh->clear();
+    }
+    if (fresh->empty()) {
+        std::string log;
+        rc = compile_cubin(prog_seed, dag_items, *fresh, log);
+        if (rc == NX_OK && !path.empty()) {
+            // several processes (one per GPU) may compile the same period at the same time: write beside the
+            // final name and rename, so that no reader ever sees a half-written cubin
+            const std::string tmp = path + ".tmp." + std::to_string((long)getpid());
+            bool ok = false;
+            {
+                std::ofstream f(tmp, std::ios::binary);
+                f.write(fresh->data(), (std::streamsize)fresh->size());
+                ok = f.good();
+            }
+            if (!ok || std::rename(tmp.c_str(), path.c_str()) != 0) std::remove(tmp.c_str());
+        }
+    }
+    {
+        std::lock_guard<std::mutex> lk(g_compile_mu);
+        if (rc == NX_OK) {
+            while (g_cubins.size() >= 8) g_cubins.erase(g_cubins.begin());  // lowest period first: heights ascend
+            g_cubins[ckey] = fresh;
+            *out = fresh;
+        }
+        g_inflight.erase(ckey);
+    }
+    mine.set_value(rc);
+    return rc;
+}
+
+// The period changes every 3 blocks.  A caller that searches period p will want p+1 within minutes, and compiling it
+// then would stall its first call by the whole NVRTC run; so the first use of a period starts the compilation of the
+// next one on a background thread (one at a time; NX_NO_PREFETCH=1 turns it off).  Only the device-independent cubin
+// is prepared: loading it into a device later takes about 0.1 ms.  Callers that plan ahead themselves
+// (nx_kawpow_prepare, nx_miner_prepare_async) find the work already done or in progress.
+namespace
+{
+struct Prefetch
+{
+    std::mutex mu;
+    std::future<void> fut;
+    ~Prefetch()
+    {
+        if (fut.valid()) fut.wait();  // never leave NVRTC running while the process tears down
+    }
+} g_prefetch;
+}  // namespace
+
+static void prefetch_next_period(int device, uint64_t prog_seed, uint32_t dag_items)
+{
+    static const bool off = [] {
+        const char* e = std::getenv("NX_NO_PREFETCH");
+        return e && *e && *e != '0';
+    }();
+    if (off) return;
+    const uint64_t next = prog_seed + 1;
+    if ((next * NX_PERIOD_LENGTH) / NX_EPOCH_LENGTH != (prog_seed * NX_PERIOD_LENGTH) / NX_EPOCH_LENGTH) return;  // next epoch: other DAG size
+    // only where periods are used in ascending order (a chain being mined or followed), or the same one again: a caller
+    // that walks heights downwards or at random would get nothing from it
+    static std::atomic<uint64_t> last_seed{~0ull};
+    const uint64_t prev = last_seed.exchange(prog_seed);
+    if (!(prev == ~0ull || prev == prog_seed || prev + 1 == prog_seed)) return;
+    if (kawpow_program_is_cached(device, next, dag_items)) return;
+    {
+        std::lock_guard<std::mutex> lk(g_compile_mu);
+        if (g_cubins.count(std::make_pair(next, dag_items)) || g_inflight.count(std::make_pair(next, dag_items))) return;
+    }
+    std::lock_guard<std::mutex> lk(g_prefetch.mu);
+    if (g_prefetch.fut.valid() && g_prefetch.fut.wait_for(std::chrono::seconds(0)) != std::future_status::ready) return;
+    g_prefetch.fut = std::async(std::launch::async, [next, dag_items] {
+        std::shared_ptr<const std::vector<char>> drop;
+        obtain_cubin(next, dag_items, &drop);  // a failure here is the foreground call's to report when it gets there
+        clear_error();
+    });
+}
+
 // Three steps with separate locks, so that a cached lookup (every search call makes one) never waits behind another
 // thread's compilation of the next period: (1) map lookup under g_cache_mu; (2) cubin for (prog_seed, dag_items) under
 // g_compile_mu - one NVRTC run serves every device of the process; (3) per-device module load, then publish.
@@ -253,42 +374,8 @@ static int get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
     const auto t0 = std::chrono::steady_clock::now();
     std::shared_ptr<const std::vector<char>> cubin;
     {
-        std::lock_guard<std::mutex> lk(g_compile_mu);
-        const auto ckey = std::make_pair(prog_seed, dag_items);
-        auto it = g_cubins.find(ckey);
-        if (it != g_cubins.end()) {
-            cubin = it->second;
-        } else {
-            auto fresh = std::make_shared<std::vector<char>>();
-            const char* arch_env = std::getenv("NX_KAWPOW_ARCH");
-            const std::string path = cache_path(prog_seed, dag_items, arch_env && *arch_env ? arch_env : "sm_100a");
-            if (!path.empty()) {
-                std::ifstream f(path, std::ios::binary);
-                if (f) fresh->assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
-                // a file that is not a whole ELF image (foreign, truncated by a crash) is ignored and rewritten
-                if (fresh->size() < 64 || std::memcmp(fresh->data(), "\x7f" "ELF", 4) != 0) fresh->clear();
-            }
-            if (fresh->empty()) {
-                std::string log;
-                const int rc = compile_cubin(prog_seed, dag_items, *fresh, log);
-                if (rc != NX_OK) return rc;
-                if (!path.empty()) {
-                    // several processes (one per GPU) may compile the same period at the same time: write beside the
-                    // final name and rename, so that no reader ever sees a half-written cubin
-                    const std::string tmp = path + ".tmp." + std::to_string((long)getpid());
-                    bool ok = false;
-                    {
-                        std::ofstream f(tmp, std::ios::binary);
-                        f.write(fresh->data(), (std::streamsize)fresh->size());
-                        ok = f.good();
-                    }
-                    if (!ok || std::rename(tmp.c_str(), path.c_str()) != 0) std::remove(tmp.c_str());
-                }
-            }
-            while (g_cubins.size() >= 8) g_cubins.erase(g_cubins.begin());  // lowest period first: heights ascend
-            g_cubins[ckey] = fresh;
-            cubin = fresh;
-        }
+        const int rc = obtain_cubin(prog_seed, dag_items, &cubin);
+        if (rc != NX_OK) return rc;
     }
     std::shared_ptr<KawpowProgram> p(new KawpowProgram);
     p->device = device;
@@ -339,7 +426,11 @@ static int get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::
 
 int kawpow_get_program(int device, uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<KawpowProgram>* out)
 {
-    return guarded([&] { return get_program(device, prog_seed, dag_items, out); });
+    return guarded([&] {
+        const int rc = get_program(device, prog_seed, dag_items, out);
+        if (rc == NX_OK) prefetch_next_period(device, prog_seed, dag_items);
+        return rc;
+    });
 }
 
 // Shape of one launch.  A unit is the work one warp does between two looks at the job: 2 x per_hw nonces (one
