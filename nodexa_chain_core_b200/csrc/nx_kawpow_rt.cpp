@@ -237,6 +237,7 @@ bool kawpow_program_is_cached(int device, uint64_t prog_seed, uint32_t dag_items
 namespace
 {
 std::map<std::pair<uint64_t, uint32_t>, std::shared_future<int>> g_inflight;
+std::atomic<bool> g_nvrtc_used{false};  // NVRTC has compiled something in this process (its lazy state exists)
 }
 
 static int obtain_cubin(uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<const std::vector<char>>* out)
@@ -277,6 +278,7 @@ static int obtain_cubin(uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<
     if (fresh->empty()) {
         std::string log;
         rc = compile_cubin(prog_seed, dag_items, *fresh, log);
+        if (rc == NX_OK) g_nvrtc_used.store(true);
         if (rc == NX_OK && !path.empty()) {
             // several processes (one per GPU) may compile the same period at the same time: write beside the
             // final name and rename, so that no reader ever sees a half-written cubin
@@ -304,30 +306,35 @@ static int obtain_cubin(uint64_t prog_seed, uint32_t dag_items, std::shared_ptr<
 }
 
 // The period changes every 3 blocks.  A caller that searches period p will want p+1 within minutes, and compiling it
-// then would stall its first call by the whole NVRTC run; so the first use of a period starts the compilation of the
-// next one on a background thread (one at a time; NX_NO_PREFETCH=1 turns it off).  Only the device-independent cubin
-// is prepared: loading it into a device later takes about 0.1 ms.  Callers that plan ahead themselves
-// (nx_kawpow_prepare, nx_miner_prepare_async) find the work already done or in progress.
+// then stalls its first call by the whole NVRTC run.  With NX_PREFETCH=1 the use of a period starts the compilation of
+// the next one on a background thread (one at a time; only the device-independent cubin: loading it into a device
+// later takes about 0.1 ms).  Opt-in, because a thread that is inside NVRTC when the process exits races the
+// library's own teardown: the wait for it is registered with atexit() at the first prefetch, which runs before the
+// destructors of everything constructed earlier - so a prefetch only starts once NVRTC has compiled something in the
+// foreground (its lazily built state then predates the registration).  Callers that plan ahead themselves
+// (nx_kawpow_prepare, nx_miner_prepare_async) need none of this.
 namespace
 {
 struct Prefetch
 {
     std::mutex mu;
     std::future<void> fut;
-    ~Prefetch()
+    void wait()
     {
-        if (fut.valid()) fut.wait();  // never leave NVRTC running while the process tears down
+        std::lock_guard<std::mutex> lk(mu);
+        if (fut.valid()) fut.wait();
     }
+    ~Prefetch() { wait(); }
 } g_prefetch;
 }  // namespace
 
 static void prefetch_next_period(int device, uint64_t prog_seed, uint32_t dag_items)
 {
-    static const bool off = [] {
-        const char* e = std::getenv("NX_NO_PREFETCH");
+    static const bool on = [] {
+        const char* e = std::getenv("NX_PREFETCH");
         return e && *e && *e != '0';
     }();
-    if (off) return;
+    if (!on || !g_nvrtc_used.load()) return;
     const uint64_t next = prog_seed + 1;
     if ((next * NX_PERIOD_LENGTH) / NX_EPOCH_LENGTH != (prog_seed * NX_PERIOD_LENGTH) / NX_EPOCH_LENGTH) return;  // next epoch: other DAG size
     // only where periods are used in ascending order (a chain being mined or followed), or the same one again: a caller
@@ -340,6 +347,8 @@ static void prefetch_next_period(int device, uint64_t prog_seed, uint32_t dag_it
         std::lock_guard<std::mutex> lk(g_compile_mu);
         if (g_cubins.count(std::make_pair(next, dag_items)) || g_inflight.count(std::make_pair(next, dag_items))) return;
     }
+    static std::once_flag at_exit;
+    std::call_once(at_exit, [] { std::atexit([] { g_prefetch.wait(); }); });  // before any teardown, see above
     std::lock_guard<std::mutex> lk(g_prefetch.mu);
     if (g_prefetch.fut.valid() && g_prefetch.fut.wait_for(std::chrono::seconds(0)) != std::future_status::ready) return;
     g_prefetch.fut = std::async(std::launch::async, [next, dag_items] {

@@ -133,7 +133,7 @@ def test_program_cache_dir_persists_compiled_periods(tmp_path):
     from conftest import ROOT
     code = ("import nodexa_chain_core_b200 as nx; from nodexa_chain_core_b200 import progpow;"
             "c = nx.create_epoch_context(0, 0); print(progpow.hash_batch(c, 300, bytes(32), 0, 4).hex()); c.close()")
-    env = dict(os.environ, NX_PROGRAM_CACHE_DIR=str(tmp_path), NX_VERBOSE="1", NX_NO_PREFETCH="1")  # this period only
+    env = dict(os.environ, NX_PROGRAM_CACHE_DIR=str(tmp_path), NX_VERBOSE="1")
     first = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
     assert first.returncode == 0, first.stderr[-2000:]
     files = sorted(os.listdir(tmp_path))
@@ -155,45 +155,51 @@ def test_program_cache_dir_persists_compiled_periods(tmp_path):
     assert sorted(os.listdir(tmp_path)) == files and len(open(path, "rb").read()) == len(good)
 
 
-def test_next_period_is_compiled_in_the_background(nx, tmp_path):
-    """The first use of a period starts the NVRTC run of the next one on a background thread (the period changes every
-    3 blocks, progpow.hpp:21): by the time a caller gets there the cubin exists and the first call costs a module load
-    instead of a compilation.  Not across an epoch boundary (the next epoch has another DAG size)."""
+def test_next_period_is_compiled_in_the_background(tmp_path):
+    """NX_PREFETCH=1: the use of a period starts the NVRTC run of the next one on a background thread (the period
+    changes every 3 blocks, progpow.hpp:21), so that the first call of the next period costs a module load instead of a
+    compilation.  Seen from outside through the cubin directory, and through the clock; a process that exits while the
+    background run is still going waits for it first and exits cleanly."""
+    import json
     import os
     import subprocess
     import sys
-    import time
 
     from conftest import ROOT
-    # 1. across processes, seen through the cubin directory: periods 100 and 101 after one hash at height 300
-    code = ("import nodexa_chain_core_b200 as nx; from nodexa_chain_core_b200 import progpow;"
-            "c = nx.create_epoch_context(0, 0); progpow.hash_batch(c, 300, bytes(32), 0, 4); c.close()")
-    env = dict(os.environ, NX_PROGRAM_CACHE_DIR=str(tmp_path))
-    env.pop("NX_NO_PREFETCH", None)
-    run = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
-    assert run.returncode == 0, run.stderr[-2000:]  # the process waited for its background compile before it exited
+    code = r"""
+import json, sys, time
+import nodexa_chain_core_b200 as nx
+from nodexa_chain_core_b200 import progpow
+c = nx.create_epoch_context(0, 0)
+t0 = time.perf_counter(); progpow.prepare(c, 6000); cold = time.perf_counter() - t0    # period 2000: a full compile
+assert len(progpow.hash_batch(c, 6000, bytes(32), 0, 4)) == 256                         # its next use starts 2001
+if sys.argv[1] == "wait":
+    time.sleep(2.0 * cold + 0.5)
+    t0 = time.perf_counter(); progpow.prepare(c, 6003); warm = time.perf_counter() - t0
+    print(json.dumps({"cold": cold, "warm": warm}))
+c.close()
+"""
+    env = dict(os.environ, NX_PROGRAM_CACHE_DIR=str(tmp_path), NX_PREFETCH="1")
+    run = subprocess.run([sys.executable, "-c", code, "wait"], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0, run.stderr[-2000:]
+    t = json.loads(run.stdout.strip().splitlines()[-1])
+    assert t["warm"] < 0.25 * t["cold"], t
     seeds = sorted(int(f.split("_")[3]) for f in os.listdir(tmp_path) if f.endswith(".cubin"))
-    assert seeds == [100, 101], seeds
-    # 2. in this process, seen through the clock: a cold period against one whose predecessor was used a moment ago
-    ctx = nx.EpochContext(0, 0)
-    try:
-        t0 = time.perf_counter()
-        progpow.prepare(ctx, 6000)        # period 2000: cold, a full compile
-        cold = time.perf_counter() - t0
-        # this process used other periods before, so one use alone says nothing about direction; the second use of the
-        # same period (a miner's next call) is what starts 2001 behind the scenes
-        assert len(progpow.hash_batch(ctx, 6000, bytes(32), 0, 4)) == 256
-        time.sleep(2.0 * cold + 0.5)      # the background run needs about as long as the foreground one did
-        t0 = time.perf_counter()
-        progpow.prepare(ctx, 6003)        # period 2001
-        warm = time.perf_counter() - t0
-        assert warm < 0.25 * cold, (warm, cold)
-        # the last period of an epoch does not prefetch into the next one
-        progpow.prepare(ctx, 7497)        # period 2499, the epoch's last
-        time.sleep(0.2)
-        assert nx.progpow.hash(ctx, 7497, bytes(32), 1).final_hash != bytes(32)
-    finally:
-        ctx.close()
+    assert seeds[:2] == [2000, 2001], seeds
+    # exit right behind the call that started the background run: the process must wait for it and leave with rc 0
+    for f in os.listdir(tmp_path):
+        os.remove(os.path.join(tmp_path, f))
+    run = subprocess.run([sys.executable, "-c", code, "exit"], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0, (run.returncode, run.stderr[-2000:])
+    seeds = sorted(int(f.split("_")[3]) for f in os.listdir(tmp_path) if f.endswith(".cubin"))
+    assert seeds == [2000, 2001], seeds
+    # without the switch nothing is compiled ahead
+    for f in os.listdir(tmp_path):
+        os.remove(os.path.join(tmp_path, f))
+    env.pop("NX_PREFETCH")
+    run = subprocess.run([sys.executable, "-c", code, "exit"], cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0
+    assert sorted(int(f.split("_")[3]) for f in os.listdir(tmp_path) if f.endswith(".cubin")) == [2000]
 
 
 def test_chain_across_period_switches_and_an_epoch_boundary(nx, oracle):
