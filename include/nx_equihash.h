@@ -34,6 +34,13 @@ void nx_equihash_destroy(nx_equihash* solver);
 int nx_equihash_solve(nx_equihash* solver, const uint8_t* header, size_t header_len, uint8_t* solutions_out,
                       int max_solutions, int* n_solutions);
 
+/* The same for n headers of header_len bytes each, laid end to end, with two solves kept in flight (a second set of device
+ * buffers is created on the first call): counts[i] receives the number of solutions of header i, solutions_out their
+ * encodings in header order (each header's sorted, without duplicates), at most max_solutions_total of them; *wall_ms (may
+ * be NULL) the host time of the whole call.  nx_equihash_last_dropped / _candidates then refer to the whole batch. */
+int nx_equihash_solve_batch(nx_equihash* solver, const uint8_t* headers, size_t header_len, int n, uint8_t* solutions_out,
+                            int max_solutions_total, int* counts, float* wall_ms);
+
 /* GPU-side validator: recomputes the BLAKE2b strings of `count` claimed solutions of one header and re-checks the
  * collisions of every round, the ordering rule, distinctness and the final zero XOR.  verdict[i] = 1 / 0. */
 int nx_equihash_validate(nx_equihash* solver, const uint8_t* header, size_t header_len, const uint8_t* solutions,

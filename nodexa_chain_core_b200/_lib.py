@@ -151,6 +151,7 @@ def _load() -> C.CDLL:
         "nx_equihash_create": (i, [i, i, i, u8p, C.POINTER(vp)]),
         "nx_equihash_destroy": (None, [vp]),
         "nx_equihash_solve": (i, [vp, u8p, sz, u8p, i, C.POINTER(i)]),
+        "nx_equihash_solve_batch": (i, [vp, u8p, sz, i, u8p, i, C.POINTER(i), C.POINTER(C.c_float)]),
         "nx_equihash_validate": (i, [vp, u8p, sz, u8p, i, u8p]),
         "nx_equihash_last_dropped": (i, [vp]),
         "nx_equihash_last_candidates": (i, [vp]),

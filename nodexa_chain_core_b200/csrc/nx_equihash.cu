@@ -25,6 +25,7 @@
 #include "nx_internal.hpp"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
@@ -540,6 +541,7 @@ struct nx_equihash
     uint32_t last_candidates = 0;
     uint32_t last_dropped = 0;  // rows/candidates lost to a full bucket in the last solve (0 in normal operation)
     bool counters_clean = false;  // both slot-counter arrays are known to be all zero
+    nx_equihash* twin = nullptr;     // second instance of the same solver, created by the first nx_equihash_solve_batch
     uint32_t* host_first = nullptr;  // pinned: {valid[F], indices[F x 2^k], stats[2]} of the first F candidates, one async copy each
     std::mutex mu;
 };
@@ -556,6 +558,7 @@ size_t nx_equihash_solution_bytes(int n, int k)
 void nx_equihash_destroy(nx_equihash* s)
 {
     if (!s) return;
+    if (s->twin) nx_equihash_destroy(s->twin);
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     for (int i = 0; i < 2; ++i) {
@@ -645,18 +648,11 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     return NX_OK;
 }
 
-// All solutions of one header (header = everything that is hashed before the LE32 string counter, nonce included;
-// its length must be a multiple of 4).  solutions_out receives up to max_solutions minimal encodings, sorted
-// bytewise; *n_solutions the number found.
-int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, uint8_t* solutions_out, int max_solutions,
-                      int* n_solutions)
+// One solve in two halves, so that two solver instances can be kept in flight (nx_equihash_solve_batch): eq_begin queues
+// everything on the instance's stream - generator, k rounds, the first candidate expansion, the copies of its results -
+// and returns; eq_end waits for it and turns the candidates into encoded solutions.
+static int eq_begin(nx_equihash* s, const uint8_t* header, size_t header_len)
 {
-    if (!s || !header || !n_solutions || (!solutions_out && max_solutions > 0)) {
-        set_error("null argument");
-        return NX_ERR_INVALID;
-    }
-    *n_solutions = 0;
-    std::lock_guard<std::mutex> lk(s->mu);
     NX_CUDA(cudaSetDevice(s->device));
     const EqParams& p = s->p;
     EqMid mid;
@@ -707,24 +703,40 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     NX_CUDA(cudaMemcpyAsync(h_valid, s->cand_valid, (size_t)EQ_RECOVER_FIRST * 4, cudaMemcpyDeviceToHost, s->stream));
     NX_CUDA(cudaMemcpyAsync(h_idx, s->cand_indices, (size_t)EQ_RECOVER_FIRST * leaves * 4, cudaMemcpyDeviceToHost, s->stream));
     NX_CUDA(cudaMemcpyAsync(stats, s->cand_count, 8, cudaMemcpyDeviceToHost, s->stream));
+    s->last_launches = launches;
+    return NX_OK;
+}
+
+static int eq_end(nx_equihash* s, std::vector<std::vector<uint8_t>>& sols)
+{
+    sols.clear();
+    NX_CUDA(cudaSetDevice(s->device));
+    const EqParams& p = s->p;
+    const int k = p.k;
+    const uint32_t leaves = 1u << k;
+    uint32_t* const h_valid = s->host_first;
+    uint32_t* const h_idx = s->host_first + EQ_RECOVER_FIRST;
+    uint32_t* const stats = s->host_first + (size_t)EQ_RECOVER_FIRST * (leaves + 1);
     NX_CUDA(cudaStreamSynchronize(s->stream));
     s->counters_clean = true;
     s->last_dropped = stats[1] + (stats[0] > EQ_MAX_CANDIDATES ? stats[0] - EQ_MAX_CANDIDATES : 0);
     const uint32_t ncand = std::min<uint32_t>(stats[0], EQ_MAX_CANDIDATES);
     NX_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
     if (ncand > EQ_RECOVER_FIRST) {
+        EqTrees trees;
+        for (int i = 0; i < EQ_MAX_CHUNKS; ++i) trees.t[i] = s->tree[i];
+        trees.leaf = s->leaf;
         NX_CUDA(cudaEventRecord(s->ev0, s->stream));
         eq_recover_kernel<<<ncand - EQ_RECOVER_FIRST, leaves, 0, s->stream>>>(p, trees, s->cand_count, EQ_MAX_CANDIDATES,
                                                                              EQ_RECOVER_FIRST, s->cand_indices, s->cand_valid);
         NX_CUDA(cudaGetLastError());
-        ++launches;
+        ++s->last_launches;
         NX_CUDA(cudaEventRecord(s->ev1, s->stream));
         NX_CUDA(cudaStreamSynchronize(s->stream));
         float more = 0;
         NX_CUDA(cudaEventElapsedTime(&more, s->ev0, s->ev1));
         s->last_ms += more;
     }
-    s->last_launches = launches;
     s->last_candidates = ncand;
     if (ncand == 0) return NX_OK;
     std::vector<uint32_t> valid(ncand), idx((size_t)ncand * leaves);
@@ -737,7 +749,6 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
                            (size_t)(ncand - have) * leaves * 4, cudaMemcpyDeviceToHost));
     }
     const size_t sb = ((size_t)1 << k) * (size_t)(p.cbl + 1) / 8;
-    std::vector<std::vector<uint8_t>> sols;
     for (uint32_t c = 0; c < ncand; ++c) {
         if (!valid[c]) continue;
         std::vector<uint8_t> enc(sb, 0);
@@ -749,9 +760,85 @@ int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, 
     }
     std::sort(sols.begin(), sols.end());
     sols.erase(std::unique(sols.begin(), sols.end()), sols.end());
-    *n_solutions = (int)sols.size();
-    for (size_t i = 0; i < sols.size() && (int)i < max_solutions; ++i) std::memcpy(solutions_out + i * sb, sols[i].data(), sb);
     return NX_OK;
+}
+
+// All solutions of one header (header = everything that is hashed before the LE32 string counter, nonce included;
+// its length must be a multiple of 4).  solutions_out receives up to max_solutions minimal encodings, sorted
+// bytewise; *n_solutions the number found.
+int nx_equihash_solve(nx_equihash* s, const uint8_t* header, size_t header_len, uint8_t* solutions_out, int max_solutions,
+                      int* n_solutions)
+{
+    if (!s || !header || !n_solutions || (!solutions_out && max_solutions > 0)) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    *n_solutions = 0;
+    return guarded([&]() -> int {
+        std::lock_guard<std::mutex> lk(s->mu);
+        int rc = eq_begin(s, header, header_len);
+        if (rc != NX_OK) return rc;
+        std::vector<std::vector<uint8_t>> sols;
+        if ((rc = eq_end(s, sols)) != NX_OK) return rc;
+        const size_t sb = nx_equihash_solution_bytes(s->p.n, s->p.k);
+        *n_solutions = (int)sols.size();
+        for (size_t i = 0; i < sols.size() && (int)i < max_solutions; ++i) std::memcpy(solutions_out + i * sb, sols[i].data(), sb);
+        return NX_OK;
+    });
+}
+
+// Solutions of n headers of equal length, two solves in flight: while one instance's kernels run, the other's results
+// are decoded on the host and its next header is queued, so the GPU never waits for the host between nonces and the
+// thin tail of one solve (candidate expansion, the last narrow rounds) overlaps the wide start of the next.
+// counts[i] = solutions of header i; their encodings follow each other in solutions_out (header order, each header's
+// sorted), as many as max_solutions_total allows.  The second instance (another set of row buffers) is created on the
+// first call and lives as long as the solver.
+int nx_equihash_solve_batch(nx_equihash* s, const uint8_t* headers, size_t header_len, int n, uint8_t* solutions_out,
+                            int max_solutions_total, int* counts, float* wall_ms)
+{
+    if (!s || (n > 0 && (!headers || !counts)) || (!solutions_out && max_solutions_total > 0) || n < 0) {
+        set_error("null argument");
+        return NX_ERR_INVALID;
+    }
+    return guarded([&]() -> int {
+        std::lock_guard<std::mutex> lk(s->mu);
+        if (!s->twin) {
+            const int rc = nx_equihash_create(s->device, s->p.n, s->p.k, s->tag, &s->twin);
+            if (rc != NX_OK) return rc;
+            s->twin->p.cnt_stride = s->p.cnt_stride;
+        }
+        nx_equihash* lane[2] = {s, s->twin};
+        const size_t sb = nx_equihash_solution_bytes(s->p.n, s->p.k);
+        const auto t0 = std::chrono::steady_clock::now();
+        int written = 0;
+        uint32_t dropped = 0, cands = 0;
+        std::vector<std::vector<uint8_t>> sols;
+        auto finish = [&](int i) -> int {  // header i ran on lane i & 1
+            const int rc = eq_end(lane[i & 1], sols);
+            if (rc != NX_OK) return rc;
+            counts[i] = (int)sols.size();
+            dropped += lane[i & 1]->last_dropped;
+            cands += lane[i & 1]->last_candidates;
+            for (size_t q = 0; q < sols.size() && written < max_solutions_total; ++q, ++written)
+                std::memcpy(solutions_out + (size_t)written * sb, sols[q].data(), sb);
+            return NX_OK;
+        };
+        for (int i = 0; i < n; ++i) {
+            int rc;
+            if (i >= 2 && (rc = finish(i - 2)) != NX_OK) return rc;
+            if ((rc = eq_begin(lane[i & 1], headers + (size_t)i * header_len, header_len)) != NX_OK) return rc;
+        }
+        for (int i = n >= 2 ? n - 2 : 0; i < n; ++i) {
+            const int rc = finish(i);
+            if (rc != NX_OK) return rc;
+        }
+        const float ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        if (wall_ms) *wall_ms = ms;
+        s->last_ms = ms;
+        s->last_dropped = dropped;
+        s->last_candidates = cands;
+        return NX_OK;
+    });
 }
 
 // GPU-side validator for `count` encoded solutions of one header: verdict[i] = 1 when solution i is valid.

@@ -26,6 +26,28 @@ class Solver:
         raw = bytes(out)
         return [raw[i * self.solution_bytes:(i + 1) * self.solution_bytes] for i in range(min(cnt.value, max_solutions))]
 
+    def solve_batch(self, headers, max_solutions_total: int = 0) -> list:
+        """Solutions of several headers of equal length, two solves in flight on the GPU: [[solution, ...], ...] in
+        header order.  last_wall_ms is the host time of the whole call."""
+        headers = list(headers)
+        if not headers:
+            return []
+        hl = len(headers[0])
+        if any(len(h) != hl for h in headers):
+            raise ValueError("headers of one batch must have the same length")
+        cap = max_solutions_total or 16 * len(headers)
+        out = outb(self.solution_bytes * cap)
+        counts = (C.c_int * len(headers))()
+        ms = C.c_float()
+        check(lib.nx_equihash_solve_batch(self._h, inb(b"".join(headers)), hl, len(headers), out, cap, counts, C.byref(ms)))
+        self.last_wall_ms = ms.value
+        raw, res, pos = bytes(out), [], 0
+        for c in counts:
+            take = max(0, min(c, cap - pos))
+            res.append([raw[(pos + j) * self.solution_bytes:(pos + j + 1) * self.solution_bytes] for j in range(take)])
+            pos += take
+        return res
+
     def validate(self, header: bytes, solutions) -> list:
         solutions = list(solutions)
         if not solutions:

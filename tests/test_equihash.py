@@ -103,3 +103,29 @@ def test_equihash_rejects_unsupported_parameters(nx):
         assert nx.lib.nx_equihash_create(0, n, k, (C.c_uint8 * 8)(*TAG), C.byref(h)) == -1 and not h.value
         assert nx.lib.nx_equihash_solution_bytes(n, k) == 0
     assert nx.lib.nx_equihash_solution_bytes(200, 9) == 1344 and nx.lib.nx_equihash_solution_bytes(144, 5) == 100
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,k,count", [(96, 5, 9), (200, 9, 12)])
+def test_batch_of_headers_equals_one_at_a_time(nx, gpu, n, k, count):
+    """nx_equihash_solve_batch keeps two solves in flight on two sets of device buffers: per header it must return exactly
+    what nx_equihash_solve returns (same solutions, same order), for odd and even batch lengths, a batch of one, an empty
+    batch, and when the output array is too small for everything."""
+    hdrs = [_header(1000 + i) for i in range(count)]
+    with nx.equihash.Solver(n, k, TAG) as s:
+        single = [s.solve(h) for h in hdrs]
+        assert any(single), "no header of the batch has a solution: pick other nonces"
+        assert s.solve_batch(hdrs) == single
+        assert s.last_dropped == 0 and s.last_wall_ms > 0
+        assert s.solve_batch(hdrs[:count - 1]) == single[:count - 1]
+        assert s.solve_batch(hdrs[:1]) == single[:1]
+        assert s.solve_batch([]) == []
+        assert [s.solve(h) for h in hdrs[:3]] == single[:3]          # the single-header path still works afterwards
+        total = sum(len(x) for x in single)
+        if total >= 2:
+            got = s.solve_batch(hdrs, max_solutions_total=total - 1)  # one slot short: the last solution is cut, counts are not
+            assert sum(len(x) for x in got) == total - 1
+            flat = [y for x in single for y in x]
+            assert [y for x in got for y in x] == flat[:total - 1]
+        with pytest.raises(ValueError):
+            s.solve_batch([hdrs[0], hdrs[1] + b"\0\0\0\0"])

@@ -40,6 +40,13 @@ def main():
             run = {"n": n, "k": k, "nonces": a.nonces, "solutions": sols, "sol_per_s_device": sols / (kernel_ms * 1e-3),
                    "sol_per_s_e2e": sols / wall, "ms_per_nonce_device": kernel_ms / a.nonces, "ms_per_nonce_e2e": wall / a.nonces * 1e3,
                    "launches_per_nonce": s.last_timing()[1], "rows_dropped": dropped, "candidates": cands}
+            # the same headers as one batch: two solves in flight, host decoding overlapped (wall clock of the whole call)
+            s.solve_batch([header(10**6 + w) for w in range(4)])
+            t0 = time.perf_counter()
+            got = s.solve_batch([header(i) for i in range(a.nonces)])
+            wall_b = time.perf_counter() - t0
+            run.update(batch_solutions=sum(len(x) for x in got), sol_per_s_batch_e2e=sum(len(x) for x in got) / wall_b,
+                       ms_per_nonce_batch_e2e=wall_b / a.nonces * 1e3, batch_rows_dropped=s.last_dropped)
             res["runs"].append(run)
     print(json.dumps(res))
 
