@@ -6,6 +6,8 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/f_sm
 echo "smoke rc=$?" > gpurun_out/f_status.txt
 timeout 1200 python -m pytest tests -x -q -m gpu > gpurun_out/f_pytest_gpu.log 2>&1
 echo "pytest gpu rc=$?" >> gpurun_out/f_status.txt
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q -m gpu > gpurun_out/f_pytest_noalloc_alone.log 2>&1
+echo "pytest no-alloc alone rc=$?" >> gpurun_out/f_status.txt
 timeout 600 python bench.py --impl reference --steps 20 --warmup 3 > gpurun_out/f_bench_ref.json 2> gpurun_out/f_bench_ref.err
 echo "bench reference rc=$?" >> gpurun_out/f_status.txt
 timeout 600 python bench.py --gpus 1 --steps 20 --warmup 3 > gpurun_out/f_bench_n1_steps20.json 2> gpurun_out/f_bench_n1.err
