@@ -639,11 +639,6 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
         nx_equihash_destroy(s);
         return NX_ERR_OOM;
     }
-    if (const char* e = std::getenv("NX_EQ_SWAP"))  // experiment: which ping-pong buffer is read first
-        {
-            if (*e == '1' || *e == '3') std::swap(s->rows[0], s->rows[1]);
-            if (*e == '1' || *e == '2') std::swap(s->bucket_cnt[0], s->bucket_cnt[1]);
-        }
     *out = s;
     return NX_OK;
 }
