@@ -204,7 +204,7 @@ __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
 // onto the chain of its key (one shared-memory atomicExch per row: head[key] <- row, next[row] <- old head); a row
 // then pairs with everything behind it in its chain.  (Round 1 counting-sorted the bucket instead: two shared-memory
 // atomics per row, a 256-bin scan and three more barriers - the atomics alone were a third of a round.)
-// dynamic shared memory: [the bucket's rows without their sort key: slots x eq_smem_stride(S) words][pre: slots x u32][next: slots x u16]
+// dynamic shared memory: [the bucket's rows without their sort key: slots x eq_smem_stride(S) words][next: slots x u16]
 template <int S>
 __global__ void __launch_bounds__(EQ_COLLIDE_THREADS, EQ_COLLIDE_BLOCKS(S))
 eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t* __restrict__ bucket_cnt,
@@ -213,7 +213,6 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
 {
     extern __shared__ __align__(16) uint32_t eq_smem[];
     __shared__ uint32_t head[256];
-    __shared__ uint32_t warp_sum[EQ_COLLIDE_THREADS / 32 + 1];
     constexpr uint32_t NIL = 0xffffu;
     constexpr uint32_t ST = (S + 3) & ~3;         // stride of the rows read
     constexpr uint32_t SO = S - 1;                // live words of the rows written (word 0 = chunk r + 1)
@@ -221,8 +220,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
     constexpr uint32_t SP = eq_smem_stride(S);    // stride of a row in shared memory (even where that is free: 8/16-byte reads)
     // shared memory keeps only what a pair needs: the SO words behind the sort key (word 0 picks the chain and is done)
     uint32_t* const rs = eq_smem;
-    uint32_t* const pre = eq_smem + (size_t)p.slots * SP;  // pairs before row i (exclusive prefix sum), see below
-    uint16_t* const next = reinterpret_cast<uint16_t*>(pre + p.slots);
+    uint16_t* const next = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SP);
     const uint32_t b = blockIdx.x, t = threadIdx.x;
     const uint32_t cnt = min(bucket_cnt[b * p.cnt_stride], p.slots);
     head[t] = NIL;
@@ -266,106 +264,75 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
         }
     }
     __syncthreads();
-    // Row i pairs with every row behind it in its chain.  Chains are a few rows long on average but the longest of a
-    // bucket reaches 7-8, and a thread that walked its own rows' chains would need that many round trips to the slot
-    // counters while its neighbours idle (a third of the kernel's stall samples sat on the returned slots).  So the
-    // pairs are numbered first - pairs of row i = rows behind it, an exclusive prefix sum over the bucket's rows - and
-    // then dealt out evenly: thread t takes pairs t, t+256, ..., finds a pair's first row by binary search in the prefix
-    // sums and its second by stepping along the chain.  A bucket has 500-600 pairs, so EQ_CURSORS pairs per thread
-    // cover it in one step: all XORs, then all slot reservations in flight together, then all stores.
-    {
-        uint32_t mine = 0;
-        for (uint32_t i = t; i < cnt; i += EQ_COLLIDE_THREADS) {
-            uint32_t q = 0;
-            for (uint32_t j = next[i]; j != NIL; j = next[j]) ++q;
-            pre[i] = q;
-            mine += q;
-        }
-        (void)mine;
-    }
-    __syncthreads();
-    {   // exclusive prefix sum of pre[0..cnt): thread t owns the contiguous rows [t*R, (t+1)*R)
-        const uint32_t R = (cnt + EQ_COLLIDE_THREADS - 1) / EQ_COLLIDE_THREADS;
-        const uint32_t lo = t * R, hi = min(lo + R, cnt);
-        uint32_t sum = 0;
-        for (uint32_t i = lo; i < hi; ++i) sum += pre[i];
-        uint32_t inc = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
-            if ((t & 31u) >= (uint32_t)o) inc += u;
-        }
-        if ((t & 31u) == 31u) warp_sum[t >> 5] = inc;
-        __syncthreads();
-        uint32_t off = inc - sum;
-        for (uint32_t w = 0; w < (t >> 5); ++w) off += warp_sum[w];
-        if (t == EQ_COLLIDE_THREADS - 1) warp_sum[EQ_COLLIDE_THREADS / 32] = off + sum;  // all pairs of the bucket
-        for (uint32_t i = lo; i < hi; ++i) {
-            const uint32_t q = pre[i];
-            pre[i] = off;
-            off += q;
-        }
-    }
-    __syncthreads();
-    const uint32_t n_pairs = warp_sum[EQ_COLLIDE_THREADS / 32];
-    constexpr int EQ_CURSORS = S >= 8 ? 2 : 3;  // pairs per thread and step: what the XOR results leave room for in registers
-    for (uint32_t p0 = t; p0 < n_pairs; p0 += EQ_COLLIDE_THREADS * EQ_CURSORS) {
-        uint32_t sa[EQ_CURSORS], sb[EQ_CURSORS], slot[EQ_CURSORS], nb[EQ_CURSORS];
-        uint32_t o[EQ_CURSORS][STO];
-        bool emit[EQ_CURSORS];
-        // phase A: locate the pair, XOR, decide and reserve
+    // Row i pairs with every row behind it in its chain.  A thread owns rows t, t+256, ... (EQ_CURSORS of them at a
+    // time; a bucket holds about 512 rows, so two cover it) and advances them in lock step: per step it XORs the pair of
+    // every live cursor into registers and issues the slot-reserving atomic, and only then uses the returned slots - so
+    // the atomics of a thread are in flight together (their latency is what this kernel waits on) and a pair's rows are
+    // read from shared memory once.
+    constexpr int EQ_CURSORS = 2;
+    for (uint32_t i0 = t; i0 < cnt; i0 += EQ_COLLIDE_THREADS * EQ_CURSORS) {
+        uint32_t sa[EQ_CURSORS], j[EQ_CURSORS];
+        bool live = false;
 #pragma unroll
         for (int c = 0; c < EQ_CURSORS; ++c) {
-            emit[c] = false;
-            const uint32_t pr = p0 + (uint32_t)c * EQ_COLLIDE_THREADS;
-            if (pr >= n_pairs) continue;
-            uint32_t lo = 0, hi = cnt;  // the last row whose prefix is <= pr: rows without pairs share their successor's
-            while (hi - lo > 1) {       // prefix and are skipped by taking the last
-                const uint32_t mid = (lo + hi) >> 1;
-                if (pre[mid] <= pr) lo = mid; else hi = mid;
-            }
-            sa[c] = lo;
-            uint32_t j = next[lo];
-            for (uint32_t step = pr - pre[lo]; step != 0; --step) j = next[j];
-            sb[c] = j;
-            uint32_t xa[SP], xb[SP];
-            eq_load_row<SP>(rs + sa[c] * SP, xa);
-            eq_load_row<SP>(rs + sb[c] * SP, xb);
-            uint32_t any = 0;
+            const uint32_t i = i0 + (uint32_t)c * EQ_COLLIDE_THREADS;
+            sa[c] = i < cnt ? i : 0u;
+            j[c] = i < cnt ? (uint32_t)next[i] : NIL;
+            live |= j[c] != NIL;
+        }
+        while (live) {
+            uint32_t slot[EQ_CURSORS], nb[EQ_CURSORS], sb[EQ_CURSORS];
+            uint32_t o[EQ_CURSORS][STO];
+            bool emit[EQ_CURSORS];
+            // phase A: XOR, decide and reserve
 #pragma unroll
-            for (uint32_t w = 0; w < STO; ++w) {  // word w = chunk r + 1 + w
-                o[c][w] = w < SO ? (xa[w] ^ xb[w]) : 0u;
-                any |= o[c][w];
-            }
-            if (last) {
-                if (any != 0) continue;  // the last round must cancel both remaining chunks
-                if (prev_tree) {         // cheap early filter: two rows that share a child share indices
-                    const uint2 pa = prev_tree[base + sa[c]], pb = prev_tree[base + sb[c]];
-                    if (pa.x == pb.x || pa.x == pb.y || pa.y == pb.x || pa.y == pb.y) continue;
+            for (int c = 0; c < EQ_CURSORS; ++c) {
+                emit[c] = false;
+                sb[c] = j[c];
+                if (j[c] == NIL) continue;
+                uint32_t xa[SP], xb[SP];
+                eq_load_row<SP>(rs + sa[c] * SP, xa);
+                eq_load_row<SP>(rs + sb[c] * SP, xb);
+                uint32_t any = 0;
+#pragma unroll
+                for (uint32_t w = 0; w < STO; ++w) {  // word w = chunk r + 1 + w
+                    o[c][w] = w < SO ? (xa[w] ^ xb[w]) : 0u;
+                    any |= o[c][w];
                 }
-                slot[c] = atomicAdd(cand_count, 1u);
-            } else {
-                if (any == 0) continue;  // identical remainders: the two subtrees share their index set
-                nb[c] = p.bucket_bits ? (o[c][0] >> 8) : 0u;
-                slot[c] = atomicAdd(&next_cnt[nb[c] * p.cnt_stride], 1u);
+                if (last) {
+                    if (any != 0) continue;  // the last round must cancel both remaining chunks
+                    if (prev_tree) {         // cheap early filter: two rows that share a child share indices
+                        const uint2 pa = prev_tree[base + sa[c]], pb = prev_tree[base + sb[c]];
+                        if (pa.x == pb.x || pa.x == pb.y || pa.y == pb.x || pa.y == pb.y) continue;
+                    }
+                    slot[c] = atomicAdd(cand_count, 1u);
+                } else {
+                    if (any == 0) continue;  // identical remainders: the two subtrees share their index set
+                    nb[c] = p.bucket_bits ? (o[c][0] >> 8) : 0u;
+                    slot[c] = atomicAdd(&next_cnt[nb[c] * p.cnt_stride], 1u);
+                }
+                emit[c] = true;
             }
-            emit[c] = true;
-        }
-        // phase B: use the reserved slots
+            // phase B: use the reserved slots, step along the chains
+            live = false;
 #pragma unroll
-        for (int c = 0; c < EQ_CURSORS; ++c) {
-            if (!emit[c]) continue;
-            if (last) {
-                if (slot[c] < EQ_MAX_CANDIDATES) tree[slot[c]] = make_uint2(base + sa[c], base + sb[c]);
-            } else if (slot[c] >= p.slots) {
-                atomicAdd(cand_count + 1, 1u);  // a row that did not fit its bucket is lost: counted, reported
-            } else {
-                const uint32_t id = nb[c] * p.slots + slot[c];
-                uint4* dst = reinterpret_cast<uint4*>(next_rows + (size_t)id * STO);
+            for (int c = 0; c < EQ_CURSORS; ++c) {
+                if (emit[c]) {
+                    if (last) {
+                        if (slot[c] < EQ_MAX_CANDIDATES) tree[slot[c]] = make_uint2(base + sa[c], base + sb[c]);
+                    } else if (slot[c] >= p.slots) {
+                        atomicAdd(cand_count + 1, 1u);  // a row that did not fit its bucket is lost: counted, reported
+                    } else {
+                        const uint32_t id = nb[c] * p.slots + slot[c];
+                        uint4* dst = reinterpret_cast<uint4*>(next_rows + (size_t)id * STO);
 #pragma unroll
-                for (uint32_t q = 0; q < STO / 4; ++q)
-                    dst[q] = make_uint4(o[c][4 * q], o[c][4 * q + 1], o[c][4 * q + 2], o[c][4 * q + 3]);
-                tree[id] = make_uint2(base + sa[c], base + sb[c]);
+                        for (uint32_t q = 0; q < STO / 4; ++q)
+                            dst[q] = make_uint4(o[c][4 * q], o[c][4 * q + 1], o[c][4 * q + 2], o[c][4 * q + 3]);
+                        tree[id] = make_uint2(base + sa[c], base + sb[c]);
+                    }
+                }
+                if (j[c] != NIL) j[c] = next[j[c]];
+                live |= j[c] != NIL;
             }
         }
     }
@@ -663,7 +630,7 @@ int nx_equihash_create(int device, int n, int k, const uint8_t tag[8], nx_equiha
     for (int live = 2; ok && live <= p.chunks; ++live) {
         // every instantiation that will run gets its own opt-in (the 48 KiB default counts the 2 KiB of static shared
         // memory too, so sizes just below it need the attribute as well)
-        const size_t smem = (size_t)p.slots * eq_smem_stride(live) * 4 + (size_t)p.slots * 6;
+        const size_t smem = (size_t)p.slots * eq_smem_stride(live) * 4 + (size_t)p.slots * 2;
         if (smem > 40 * 1024)
             ok = cudaFuncSetAttribute(eq_collide_fn(live), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess;
     }
@@ -706,7 +673,7 @@ static int eq_begin(nx_equihash* s, const uint8_t* header, size_t header_len)
     NX_CUDA(cudaGetLastError());
     ++launches;
     for (int r = 0; r < k; ++r) {
-        const size_t smem = (size_t)p.slots * eq_smem_stride(p.chunks - r) * 4 + (size_t)p.slots * 6;
+        const size_t smem = (size_t)p.slots * eq_smem_stride(p.chunks - r) * 4 + (size_t)p.slots * 2;
         eq_collide_fn(p.chunks - r)<<<p.num_buckets, EQ_COLLIDE_THREADS, smem, s->stream>>>(
             p, r, s->rows[r & 1], s->bucket_cnt[r & 1], s->rows[(r + 1) & 1], s->bucket_cnt[(r + 1) & 1], s->tree[r + 1],
             r >= 1 ? s->tree[r] : nullptr, s->cand_count);
