@@ -222,6 +222,18 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
     uint32_t* const rs = eq_smem;
     uint16_t* const next = reinterpret_cast<uint16_t*>(eq_smem + (size_t)p.slots * SP);
     const uint32_t b = blockIdx.x, t = threadIdx.x;
+    const uint32_t base = b * p.slots;
+    constexpr uint32_t QPR = ST / 4;  // 16-byte words per row
+    constexpr uint32_t U = 4;         // row loads in flight per thread
+    const uint4* const src = reinterpret_cast<const uint4*>(rows + (size_t)base * ST);
+    // The first round of row loads is issued together with the load of the bucket's fill count instead of behind it:
+    // the slots of a bucket are all allocated, so reading past the fill is harmless, and what lies there is not used.
+    uint4 first[U];
+#pragma unroll
+    for (uint32_t u = 0; u < U; ++u) {
+        const uint32_t i = t + u * EQ_COLLIDE_THREADS;
+        first[u] = i < p.slots * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u);
+    }
     const uint32_t cnt = min(bucket_cnt[b * p.cnt_stride], p.slots);
     head[t] = NIL;
     // This CTA is the only reader of its bucket's counter, and the array it sits in is the one the NEXT round appends
@@ -229,20 +241,16 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
     __syncthreads();
     if (t == 0) bucket_cnt[b * p.cnt_stride] = 0u;
     const bool last = r == p.k - 1;
-    const uint32_t base = b * p.slots;
     if (cnt == 0) return;
 
-    {   // the bucket's rows: one contiguous region, read as 16-byte words
-        const uint4* src = reinterpret_cast<const uint4*>(rows + (size_t)base * ST);
-        constexpr uint32_t QPR = ST / 4;  // 16-byte words per row
-        // four loads in flight per thread before the first is used: the copy is a chain of global-memory latencies
-        constexpr uint32_t U = 4;
+    {   // the bucket's rows: one contiguous region, read as 16-byte words, four loads in flight per thread before the
+        // first is used (the copy is a chain of global-memory latencies)
         for (uint32_t i0 = t; i0 < cnt * QPR; i0 += EQ_COLLIDE_THREADS * U) {
             uint4 v[U];
 #pragma unroll
             for (uint32_t u = 0; u < U; ++u) {
                 const uint32_t i = i0 + u * EQ_COLLIDE_THREADS;
-                v[u] = i < cnt * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u);
+                v[u] = i0 == t ? first[u] : (i < cnt * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u));
             }
 #pragma unroll
             for (uint32_t u = 0; u < U; ++u) {
