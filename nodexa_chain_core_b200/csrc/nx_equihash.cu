@@ -228,11 +228,14 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
     const uint4* const src = reinterpret_cast<const uint4*>(rows + (size_t)base * ST);
     // The first round of row loads is issued together with the load of the bucket's fill count instead of behind it:
     // the slots of a bucket are all allocated, so reading past the fill is harmless, and what lies there is not used.
+    // Only for the wide rows: the narrow ones are compiled for 40 registers, where four more live 16-byte values spill
+    // (measured: 108 -> 104 and 84 -> 80 us for 10 and 9 words, but 68 -> 74 us for 7).
+    constexpr bool EARLY = S >= 8;
     uint4 first[U];
 #pragma unroll
     for (uint32_t u = 0; u < U; ++u) {
         const uint32_t i = t + u * EQ_COLLIDE_THREADS;
-        first[u] = i < p.slots * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u);
+        first[u] = EARLY && i < p.slots * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u);
     }
     const uint32_t cnt = min(bucket_cnt[b * p.cnt_stride], p.slots);
     head[t] = NIL;
@@ -250,7 +253,7 @@ eq_collide_kernel(EqParams p, int r, const uint32_t* __restrict__ rows, uint32_t
 #pragma unroll
             for (uint32_t u = 0; u < U; ++u) {
                 const uint32_t i = i0 + u * EQ_COLLIDE_THREADS;
-                v[u] = i0 == t ? first[u] : (i < cnt * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u));
+                v[u] = EARLY && i0 == t ? first[u] : (i < cnt * QPR ? src[i] : make_uint4(0u, 0u, 0u, 0u));
             }
 #pragma unroll
             for (uint32_t u = 0; u < U; ++u) {
