@@ -195,7 +195,9 @@ __device__ __forceinline__ void eq_load_row(const uint32_t* r, uint32_t out[SP])
 #ifndef EQ_COLLIDE_BLOCKS_NARROW
 #define EQ_COLLIDE_BLOCKS_NARROW 6
 #endif
-#define EQ_COLLIDE_BLOCKS(S) ((S) >= 8 ? 5 : EQ_COLLIDE_BLOCKS_NARROW)  // eight for rows of 5 words and fewer (32 registers) was measured too: no gain (74 vs 62 us at 5 words)  // measured: 8-word rows are slower with six (89 vs 76 us)
+// Measured alternatives: six for 8-word rows is slower (89 vs 76 us), eight for rows of 5 words and fewer (32 registers)
+// gains nothing (74 vs 62 us at 5 words).
+#define EQ_COLLIDE_BLOCKS(S) ((S) >= 8 ? 5 : EQ_COLLIDE_BLOCKS_NARROW)
 
 // ---- one round: one CTA per bucket ----
 // Rows of round r carry only the chunks that are still alive, r..k: S = chunks - r live words (template parameter, so
