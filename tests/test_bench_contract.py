@@ -44,3 +44,31 @@ def test_reference_arm_runs_on_the_host_cores():
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["cpu_baseline"]["value"] == d["value"] and d["cpu_baseline"]["kind"] in ("reference", "port")
     assert d["config"]["workload"] == "kawpow_search_epoch448"
+
+
+def test_round2_bench_lines_carry_the_extra_keys():
+    """The round-2 lines (profiles/r2_bench_n*.json) keep the base contract and add what the round-1 review asked to see in
+    the driver-run line: the epoch build per phase (both exchange routes at N>1, digest check), and the other kernels."""
+    for n in (1, 2, 4, 8):
+        d = json.loads(open(os.path.join(ROOT, "profiles", f"r2_bench_n{n}.json")).read().strip().splitlines()[-1])
+        assert BASE_KEYS | {"roofline", "clocks", "epoch_build", "paths"} <= set(d), n
+        assert d["n_gpus"] == n and d["metric"] == "KawPow MH/s" and d["warmup"] >= 3
+        assert abs(d["value"] - n * d["config"]["nonces_per_step_per_gpu"] / d["ms_per_step"] / 1e3) < 0.01 * d["value"]
+        assert 0.9 * d["value"] < d["e2e"]["value"] < 1.05 * d["value"] and d["e2e"]["h2d_bytes_per_step"] > 0
+        assert d["gpu_launches"] >= d["steps"]
+        assert not {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} & set(d["clocks"]["reasons"])
+        eb = d["epoch_build"]
+        assert eb["dag_checksum_equals_reference_digest"] is True and eb["total_s"] < 2.0
+        if n == 1:
+            assert eb["exchange"] is None and eb["allgather_ms"] is None
+            assert d["cpu_baseline"]["kind"] in ("reference", "port")
+        else:
+            assert eb["exchange"] == "fused" and eb["allgather_ms"] is None  # the exchange is inside the kernel: no separate time
+            other = eb["other_route"]
+            assert other["exchange"] == "nccl" and other["allgather_ms"] > 0 and other["total_s"] < 2.0
+        p = d["paths"]
+        assert {"K3_dag_items_kernel", "K6_kawpow_interp_kernel", "K7_ethash_hash_kernel", "nx_miner_search", "equihash_gated"} <= set(p)
+        assert 0.5 < p["K3_dag_items_kernel"]["frac_of_gather_peak"] <= 1.0
+        assert p["nx_miner_search"]["devices"] == n and p["nx_miner_search"]["mhs_wall"] > 150 * n
+        eq = p["equihash_gated"]
+        assert "not checked against the reference" in eq["parity"] and all(r["rows_dropped"] == 0 for r in eq["runs"])
